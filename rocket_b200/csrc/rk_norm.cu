@@ -1,0 +1,170 @@
+// K1: deterministic multi-tensor gradient L2 norm (HBM-bound: 4 B read per element).
+//
+// Level 1: every norm chunk (plan.chunk_norm elements of one tensor) -> one double
+//          partial, written to scratch in chunk order.
+// Level 2: the CTA that finishes last (ticket counter) reduces, in a fixed order,
+//          partials -> per-tensor norms -> total norm.  No float atomics anywhere, so
+//          the result does not depend on CTA scheduling and is bit-identical on every
+//          rank that holds the same gradients.
+#include "rk_common.cuh"
+
+#define NORM_THREADS 256
+#define NORM_WARPS (NORM_THREADS / 32)
+#define NORM_UNROLL 4
+#define NORM_BIG_TENSOR 1024  // tensors with more chunks than this are reduced block-wide
+
+__device__ __forceinline__ float sq_acc(float acc, float x, float s) {
+  float y = x * s;
+  return fmaf(y, y, acc);
+}
+
+__global__ void __launch_bounds__(NORM_THREADS)
+rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restrict__ scratch,
+                 float* __restrict__ total_out, float* __restrict__ tnorm_out) {
+  __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
+  __shared__ double s_red[2][NORM_WARPS];
+  __shared__ int s_last;
+
+  const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
+  const int n_tensors = h->n_tensors;
+  const int n_chunks = h->n_chunks_norm;
+  const int chunk = h->chunk_norm;
+  const rk_tensor_desc* descs = reinterpret_cast<const rk_tensor_desc*>(plan + h->off_descs);
+  const int32_t* gprefix = reinterpret_cast<const int32_t*>(plan + h->off_prefix_norm);
+  double* partials = reinterpret_cast<double*>(scratch + h->off_partials);
+  float* tnorms = reinterpret_cast<float*>(scratch + h->off_tnorms);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + h->off_ticket);
+
+  const int32_t* prefix = rk_stage_prefix(gprefix, n_tensors + 1, s_prefix);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  int parity = 0;
+  for (int c = blockIdx.x; c < n_chunks; c += gridDim.x, parity ^= 1) {
+    const int t = rk_find_tensor(prefix, n_tensors, c);
+    const int64_t numel = descs[t].numel;
+    const int flags = descs[t].flags;
+    const int64_t base = (int64_t)(c - prefix[t]) * chunk;
+    const int64_t rem = numel - base;
+    const int count = rem < chunk ? (int)rem : chunk;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    if (!(flags & RK_TENSOR_SKIP)) {
+      const float* __restrict__ g = descs[t].g + base;
+      if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
+        const float4* __restrict__ g4 = reinterpret_cast<const float4*>(g);
+        const int nvec = count >> 2;
+        for (int i = tid; i < nvec; i += NORM_THREADS * NORM_UNROLL) {
+          float4 x[NORM_UNROLL];
+#pragma unroll
+          for (int k = 0; k < NORM_UNROLL; ++k) {
+            const int idx = i + k * NORM_THREADS;
+            x[k] = idx < nvec ? __ldcs(g4 + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int k = 0; k < NORM_UNROLL; ++k) {
+            a0 = sq_acc(a0, x[k].x, grad_scale);
+            a1 = sq_acc(a1, x[k].y, grad_scale);
+            a2 = sq_acc(a2, x[k].z, grad_scale);
+            a3 = sq_acc(a3, x[k].w, grad_scale);
+          }
+        }
+        const int tail = nvec << 2;
+        if (tail + tid < count) a0 = sq_acc(a0, g[tail + tid], grad_scale);
+      } else {
+        for (int i = tid; i < count; i += NORM_THREADS) a0 = sq_acc(a0, g[i], grad_scale);
+      }
+    }
+    double s = (double)a0 + (double)a1 + ((double)a2 + (double)a3);
+    s = rk_warp_sum(s);
+    if (lane == 0) s_red[parity][warp] = s;
+    __syncthreads();
+    if (tid == 0) {
+      double tot = 0.0;
+#pragma unroll
+      for (int w = 0; w < NORM_WARPS; ++w) tot += s_red[parity][w];
+      partials[c] = tot;
+    }
+  }
+
+  // ---- ticket: who is last? ------------------------------------------------------
+  if (tid == 0) {
+    __threadfence();
+    unsigned int prev = atomicAdd(ticket, 1u);
+    s_last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+
+  // ---- level 2a: per-tensor norms, one warp per small tensor -----------------------
+  for (int t = warp; t < n_tensors; t += NORM_WARPS) {
+    const int c0 = gprefix[t], c1 = gprefix[t + 1];
+    if (c1 - c0 > NORM_BIG_TENSOR) continue;
+    double s = 0.0;
+    for (int c = c0 + lane; c < c1; c += 32) s += __ldcg(partials + c);
+    s = rk_warp_sum(s);
+    if (lane == 0) tnorms[t] = (float)sqrt(s);
+  }
+  // ---- level 2b: big tensors, whole CTA each ---------------------------------------
+  int par = 0;
+  for (int t = 0; t < n_tensors; ++t) {
+    const int c0 = gprefix[t], c1 = gprefix[t + 1];
+    if (c1 - c0 <= NORM_BIG_TENSOR) continue;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int c = c0 + tid;
+    for (; c + 3 * NORM_THREADS < c1; c += 4 * NORM_THREADS) {
+      s0 += __ldcg(partials + c);
+      s1 += __ldcg(partials + c + NORM_THREADS);
+      s2 += __ldcg(partials + c + 2 * NORM_THREADS);
+      s3 += __ldcg(partials + c + 3 * NORM_THREADS);
+    }
+    for (; c < c1; c += NORM_THREADS) s0 += __ldcg(partials + c);
+    double s = rk_warp_sum((s0 + s1) + (s2 + s3));
+    if (lane == 0) s_red[par][warp] = s;
+    __syncthreads();
+    if (tid == 0) {
+      double tot = 0.0;
+#pragma unroll
+      for (int w = 0; w < NORM_WARPS; ++w) tot += s_red[par][w];
+      tnorms[t] = (float)sqrt(tot);
+    }
+    par ^= 1;
+  }
+  __syncthreads();  // tnorms written by this CTA are visible to this CTA
+  // ---- level 2c: norm of the per-tensor norms (clip_grad.py:106-107) -----------------
+  double acc = 0.0;
+  for (int t = tid; t < n_tensors; t += NORM_THREADS) {
+    const float n = tnorms[t];
+    acc += (double)n * (double)n;
+    if (tnorm_out) tnorm_out[t] = n;
+  }
+  acc = rk_warp_sum(acc);
+  if (lane == 0) s_red[par][warp] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    double tot = 0.0;
+#pragma unroll
+    for (int w = 0; w < NORM_WARPS; ++w) tot += s_red[par][w];
+    const float total = (float)sqrt(tot);
+    *reinterpret_cast<float*>(scratch + h->off_total) = total;
+    if (total_out) *total_out = total;
+    *ticket = 0u;  // ready for the next launch
+  }
+}
+
+extern "C" int rk_l2norm_multi(const void* plan_host, const void* plan_dev, float grad_scale,
+                               void* scratch_dev, float* total_norm_dev,
+                               float* tensor_norms_dev, void* stream) {
+  RK_REQUIRE(plan_host && plan_dev && scratch_dev, RK_ERR_INVALID,
+             "rk_l2norm_multi: null plan or scratch");
+  const rk_plan_header* h = (const rk_plan_header*)plan_host;
+  RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "rk_l2norm_multi: bad plan magic");
+  int grid = 0;
+  int rc = rk_persistent_grid((const void*)rk_l2norm_kernel, NORM_THREADS, 0,
+                              h->n_chunks_norm, &grid);
+  if (rc) return rc;
+  rk_l2norm_kernel<<<grid, NORM_THREADS, 0, (cudaStream_t)stream>>>(
+      (const char*)plan_dev, grad_scale, (char*)scratch_dev, total_norm_dev, tensor_norms_dev);
+  RK_CUDA(cudaGetLastError());
+  g_rk_launches.fetch_add(1);
+  return 0;
+}

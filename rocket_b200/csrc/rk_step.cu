@@ -1,0 +1,296 @@
+// K2 / K3: fused multi-tensor optimizer steps (HBM-bound elementwise kernels).
+//
+// One persistent grid walks the step chunks (RK_STEP_CHUNK elements of one tensor) of
+// the whole tensor list; the chunk->tensor prefix table is staged in shared memory and
+// binary-searched per chunk.  Each thread keeps UNROLL 128-bit loads of every stream in
+// flight (p, g, m, v -> 16 independent LDG.128 for Adam) and writes p, m, v and the
+// zeroed g back with 128-bit stores: 32 B of traffic per element for the full AdamW
+// step, the algorithmic minimum.
+//
+// fp32 arithmetic is spelled with explicit round-to-nearest intrinsics in the operation
+// order of torch's CPU kernels (foreach=False), including where those use fused
+// multiply-add, so results are bit-identical to the reference's arithmetic given the
+// same gradients and clip coefficient.  See oracle/step_oracle.c for the restatement
+// this is tested against.
+#include <math.h>
+
+#include "rk_common.cuh"
+
+#define STEP_THREADS 256
+#define STEP_UNROLL 4  // 256 threads x 4 x float4 = 4096 elements = RK_STEP_CHUNK
+
+// ---- per-group constants, passed by value in kernel-parameter space ------------------
+struct AdamDev {
+  float decay;     // (float)(1 - lr*wd)         decoupled
+  float wd;        // (float)wd                  coupled (L2)
+  float w1;        // (float)(1 - beta1)
+  float w1m1;      // w1 - 1.0f                  (lerp, weight >= 0.5 branch)
+  float beta2;
+  float w2;        // (float)(1 - beta2)
+  float s2;        // (float)sqrt(bias_correction2)
+  float eps;
+  float neg_step;  // (float)(-lr / bias_correction1)
+  int flags;
+};
+#define ADAM_DECOUPLED 1
+#define ADAM_HAS_WD 2
+#define GROUP_SKIP 4
+#define ADAM_LERP_SMALL 8
+struct AdamTable { AdamDev g[RK_MAX_GROUPS]; };
+
+struct SgdDev {
+  float wd, mu, one_minus_damp, neg_lr;
+  int flags;
+};
+#define SGD_HAS_WD 1
+#define SGD_HAS_MOM 2
+#define SGD_NESTEROV 8
+#define SGD_FIRST 16
+struct SgdTable { SgdDev g[RK_MAX_GROUPS]; };
+
+struct Prolog {       // gradient pre-scaling shared by all optimizers
+  float scale;        // grad_scale (1/world_size)
+  float coef;         // clip coefficient
+  int has_scale, has_clip;
+};
+
+__device__ __forceinline__ float prolog_g(float g, const Prolog& pr) {
+  if (pr.has_scale) g = __fmul_rn(g, pr.scale);
+  if (pr.has_clip) g = __fmul_rn(g, pr.coef);  // clip_grad.py:182  g.mul_(clip_coef_clamped)
+  return g;
+}
+
+// ---- element updates -----------------------------------------------------------------
+struct AdamOp {
+  static constexpr bool kHasV = true;
+  AdamDev h;
+  __device__ __forceinline__ void operator()(float& p, float g, float& m, float& v) const {
+    if (h.flags & ADAM_HAS_WD) {
+      if (h.flags & ADAM_DECOUPLED) p = __fmul_rn(p, h.decay);  // adam.py:419
+      else g = __fmaf_rn(h.wd, p, g);                           // adam.py:430
+    }
+    const float d = __fsub_rn(g, m);                            // adam.py:457 lerp_
+    m = (h.flags & ADAM_LERP_SMALL) ? __fmaf_rn(h.w1, d, m) : __fmaf_rn(h.w1m1, d, g);
+    v = __fmaf_rn(__fmul_rn(h.w2, g), g, __fmul_rn(v, h.beta2));              // adam.py:476
+    const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), h.s2), h.eps);     // adam.py:545
+    p = __fadd_rn(p, __fdiv_rn(__fmul_rn(h.neg_step, m), denom));             // adam.py:547
+  }
+};
+
+struct SgdOp {
+  static constexpr bool kHasV = false;
+  SgdDev h;
+  __device__ __forceinline__ void operator()(float& p, float g, float& m, float&) const {
+    if (h.flags & SGD_HAS_WD) g = __fmaf_rn(h.wd, p, g);                        // sgd.py:356
+    if (h.flags & SGD_HAS_MOM) {
+      if (h.flags & SGD_FIRST) m = g;                                           // sgd.py:362
+      else m = __fmaf_rn(h.one_minus_damp, g, __fmul_rn(m, h.mu));              // sgd.py:365
+      g = (h.flags & SGD_NESTEROV) ? __fmaf_rn(h.mu, m, g) : m;                 // sgd.py:368-370
+    }
+    p = __fmaf_rn(h.neg_lr, g, p);                                              // sgd.py:380
+  }
+};
+
+// ---- the chunk walker ------------------------------------------------------------------
+template <class Op, class Table>
+__global__ void __launch_bounds__(STEP_THREADS)
+rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table table,
+               const float* __restrict__ total_norm, float max_norm, float grad_scale,
+               int zero_grads) {
+  __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
+  const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
+  const int n_tensors = h->n_tensors;
+  const int n_chunks = h->n_chunks_step;
+  const rk_tensor_desc* descs = reinterpret_cast<const rk_tensor_desc*>(plan + h->off_descs);
+  const int32_t* prefix = rk_stage_prefix(
+      reinterpret_cast<const int32_t*>(plan + h->off_prefix_step), n_tensors + 1, s_prefix);
+
+  Prolog pr;
+  pr.scale = grad_scale;
+  pr.has_scale = grad_scale != 1.0f;
+  pr.has_clip = total_norm != nullptr;
+  pr.coef = pr.has_clip ? rk_clip_coef(__ldg(total_norm), max_norm) : 1.0f;
+
+  const int tid = threadIdx.x;
+  for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+    const int t = rk_find_tensor(prefix, n_tensors, c);
+    const rk_tensor_desc d = descs[t];
+    Op op;
+    op.h = table.g[d.group];
+    if ((d.flags & RK_TENSOR_SKIP) || (op.h.flags & GROUP_SKIP)) continue;
+    const int64_t base = (int64_t)(c - prefix[t]) * RK_STEP_CHUNK;
+    const int64_t rem = d.numel - base;
+    const int count = rem < RK_STEP_CHUNK ? (int)rem : RK_STEP_CHUNK;
+    float* __restrict__ P = d.p + base;
+    float* __restrict__ G = d.g + base;
+    float* __restrict__ M = d.m + base;
+    float* __restrict__ V = Op::kHasV ? d.v + base : nullptr;
+    const bool has_m = d.m != nullptr;  // plain SGD keeps no state
+
+    if (d.flags & RK_TENSOR_VEC4) {
+      const int nvec = count >> 2;
+      float4 p4[STEP_UNROLL], g4[STEP_UNROLL], m4[STEP_UNROLL], v4[STEP_UNROLL];
+#pragma unroll
+      for (int k = 0; k < STEP_UNROLL; ++k) {
+        const int i = tid + k * STEP_THREADS;
+        if (i < nvec) {
+          p4[k] = reinterpret_cast<const float4*>(P)[i];
+          g4[k] = reinterpret_cast<const float4*>(G)[i];
+          if (has_m) m4[k] = reinterpret_cast<const float4*>(M)[i];
+          if (Op::kHasV) v4[k] = reinterpret_cast<const float4*>(V)[i];
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < STEP_UNROLL; ++k) {
+        const int i = tid + k * STEP_THREADS;
+        if (i < nvec) {
+          op(p4[k].x, prolog_g(g4[k].x, pr), m4[k].x, v4[k].x);
+          op(p4[k].y, prolog_g(g4[k].y, pr), m4[k].y, v4[k].y);
+          op(p4[k].z, prolog_g(g4[k].z, pr), m4[k].z, v4[k].z);
+          op(p4[k].w, prolog_g(g4[k].w, pr), m4[k].w, v4[k].w);
+          reinterpret_cast<float4*>(P)[i] = p4[k];
+          if (has_m) reinterpret_cast<float4*>(M)[i] = m4[k];
+          if (Op::kHasV) reinterpret_cast<float4*>(V)[i] = v4[k];
+          if (zero_grads) reinterpret_cast<float4*>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+      const int i = (nvec << 2) + tid;  // < 4 leftover elements
+      if (i < count) {
+        float p = P[i], m = has_m ? M[i] : 0.f, v = Op::kHasV ? V[i] : 0.f;
+        op(p, prolog_g(G[i], pr), m, v);
+        P[i] = p;
+        if (has_m) M[i] = m;
+        if (Op::kHasV) V[i] = v;
+        if (zero_grads) G[i] = 0.f;
+      }
+    } else {
+      for (int i = tid; i < count; i += STEP_THREADS) {
+        float p = P[i], m = has_m ? M[i] : 0.f, v = Op::kHasV ? V[i] : 0.f;
+        op(p, prolog_g(G[i], pr), m, v);
+        P[i] = p;
+        if (has_m) M[i] = m;
+        if (Op::kHasV) V[i] = v;
+        if (zero_grads) G[i] = 0.f;
+      }
+    }
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------
+static inline bool need_m(const AdamDev&) { return true; }
+static inline bool need_m(const SgdDev& g) { return (g.flags & SGD_HAS_MOM) != 0; }
+template <class Op, class Table>
+static int launch_step(const void* plan_host, const void* plan_dev, const Table& table,
+                       const float* total_norm_dev, float max_norm, float grad_scale,
+                       int zero_grads, void* stream, const char* who) {
+  RK_REQUIRE(plan_host && plan_dev, RK_ERR_INVALID, "%s: null plan", who);
+  const rk_plan_header* h = (const rk_plan_header*)plan_host;
+  RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "%s: bad plan magic", who);
+  if (h->n_chunks_step == 0) return 0;
+  {  // state pointers the chosen optimizer needs must be present
+    const rk_tensor_desc* d = (const rk_tensor_desc*)((const char*)plan_host + h->off_descs);
+    for (int i = 0; i < h->n_tensors; ++i) {
+      if ((d[i].flags & RK_TENSOR_SKIP) || d[i].numel == 0) continue;
+      const int gi = d[i].group;
+      if (table.g[gi].flags & GROUP_SKIP) continue;
+      RK_REQUIRE(!need_m(table.g[gi]) || d[i].m, RK_ERR_INVALID,
+                 "%s: tensor %d has no m (momentum / exp_avg) buffer", who, i);
+      RK_REQUIRE(!Op::kHasV || d[i].v, RK_ERR_INVALID,
+                 "%s: tensor %d has no v (exp_avg_sq) buffer", who, i);
+    }
+  }
+  int grid = 0;
+  int rc = rk_persistent_grid((const void*)rk_step_kernel<Op, Table>, STEP_THREADS, 0,
+                              h->n_chunks_step, &grid);
+  if (rc) return rc;
+  rk_step_kernel<Op, Table><<<grid, STEP_THREADS, 0, (cudaStream_t)stream>>>(
+      (const char*)plan_dev, table, total_norm_dev, max_norm, grad_scale, zero_grads);
+  RK_CUDA(cudaGetLastError());
+  g_rk_launches.fetch_add(1);
+  return 0;
+}
+
+// Host derivation of the per-group fp32 constants, in double like torch
+// ($TORCH/optim/adam.py:414-419, 529-536).  Exposed so the oracle tests can check it.
+extern "C" int rk_adam_derive(const rk_adam_group* g, float* out9, int* flags_out) {
+  RK_REQUIRE(g && out9 && flags_out, RK_ERR_INVALID, "rk_adam_derive: null argument");
+  RK_REQUIRE(g->step >= 1, RK_ERR_INVALID, "adam group: step must be >= 1 (got %lld)",
+             (long long)g->step);
+  const double step = (double)g->step;
+  const double bc1 = 1.0 - pow(g->beta1, step);
+  const double bc2 = 1.0 - pow(g->beta2, step);
+  const double step_size = g->lr / bc1;
+  const double bc2_sqrt = pow(bc2, 0.5);
+  const float w1 = (float)(1.0 - g->beta1);
+  out9[0] = (float)(1.0 - g->lr * g->weight_decay);
+  out9[1] = (float)g->weight_decay;
+  out9[2] = w1;
+  out9[3] = w1 - 1.0f;
+  out9[4] = (float)g->beta2;
+  out9[5] = (float)(1.0 - g->beta2);
+  out9[6] = (float)bc2_sqrt;
+  out9[7] = (float)g->eps;
+  out9[8] = (float)(-step_size);
+  int f = 0;
+  if (g->decoupled) f |= ADAM_DECOUPLED;
+  if (g->weight_decay != 0.0) f |= ADAM_HAS_WD;
+  if (g->skip) f |= GROUP_SKIP;
+  if (fabsf(w1) < 0.5f) f |= ADAM_LERP_SMALL;
+  *flags_out = f;
+  return 0;
+}
+
+extern "C" int rk_adamw_step_multi(const void* plan_host, const void* plan_dev,
+                                   const rk_adam_group* groups, int n_groups,
+                                   const float* total_norm_dev, float max_norm,
+                                   float grad_scale, int zero_grads, void* stream) {
+  RK_REQUIRE(groups, RK_ERR_INVALID, "rk_adamw_step_multi: null groups");
+  RK_REQUIRE(n_groups > 0 && n_groups <= RK_MAX_GROUPS, RK_ERR_TOO_LARGE,
+             "rk_adamw_step_multi: n_groups=%d outside [1,%d]", n_groups, RK_MAX_GROUPS);
+  AdamTable tab;
+  memset(&tab, 0, sizeof(tab));
+  for (int i = 0; i < RK_MAX_GROUPS; ++i) tab.g[i].flags = GROUP_SKIP;
+  for (int i = 0; i < n_groups; ++i) {
+    float c[9];
+    int f;
+    int rc = rk_adam_derive(groups + i, c, &f);
+    if (rc) return rc;
+    AdamDev& d = tab.g[i];
+    d.decay = c[0]; d.wd = c[1]; d.w1 = c[2]; d.w1m1 = c[3]; d.beta2 = c[4];
+    d.w2 = c[5]; d.s2 = c[6]; d.eps = c[7]; d.neg_step = c[8]; d.flags = f;
+  }
+  return launch_step<AdamOp, AdamTable>(plan_host, plan_dev, tab, total_norm_dev, max_norm,
+                                        grad_scale, zero_grads, stream,
+                                        "rk_adamw_step_multi");
+}
+
+extern "C" int rk_sgd_step_multi(const void* plan_host, const void* plan_dev,
+                                 const rk_sgd_group* groups, int n_groups,
+                                 const float* total_norm_dev, float max_norm,
+                                 float grad_scale, int zero_grads, void* stream) {
+  RK_REQUIRE(groups, RK_ERR_INVALID, "rk_sgd_step_multi: null groups");
+  RK_REQUIRE(n_groups > 0 && n_groups <= RK_MAX_GROUPS, RK_ERR_TOO_LARGE,
+             "rk_sgd_step_multi: n_groups=%d outside [1,%d]", n_groups, RK_MAX_GROUPS);
+  SgdTable tab;
+  memset(&tab, 0, sizeof(tab));
+  for (int i = 0; i < RK_MAX_GROUPS; ++i) tab.g[i].flags = GROUP_SKIP;
+  for (int i = 0; i < n_groups; ++i) {
+    const rk_sgd_group& g = groups[i];
+    RK_REQUIRE(!(g.nesterov && (g.momentum <= 0.0 || g.dampening != 0.0)), RK_ERR_INVALID,
+               "sgd group %d: nesterov needs momentum > 0 and dampening == 0", i);
+    SgdDev& d = tab.g[i];
+    d.wd = (float)g.weight_decay;
+    d.mu = (float)g.momentum;
+    d.one_minus_damp = (float)(1.0 - g.dampening);
+    d.neg_lr = (float)(-g.lr);
+    int f = 0;
+    if (g.weight_decay != 0.0) f |= SGD_HAS_WD;
+    if (g.momentum != 0.0) f |= SGD_HAS_MOM;
+    if (g.nesterov) f |= SGD_NESTEROV;
+    if (g.first_step) f |= SGD_FIRST;
+    if (g.skip) f |= GROUP_SKIP;
+    d.flags = f;
+  }
+  return launch_step<SgdOp, SgdTable>(plan_host, plan_dev, tab, total_norm_dev, max_norm,
+                                      grad_scale, zero_grads, stream, "rk_sgd_step_multi");
+}

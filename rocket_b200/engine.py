@@ -1,0 +1,492 @@
+"""Engine: the handle every capsule holds in ``self._accelerator``.
+
+It provides the member set the reference uses on ``accelerate.Accelerator`` (SURVEY.md
+Appendix A; reference call sites are cited per method) and implements the engine-owned work
+of the per-iteration step with the sm_100a kernels behind the C-ABI
+(include/rocket_b200.h) plus NCCL for the gradient exchange:
+
+    prepare(DataLoader)  -> EngineDataLoader : rank sharding + pinned-ring H2D staging (K5)
+    prepare(Module)      -> the module itself : param/buffer broadcast, autocast forward
+    prepare(Optimizer)   -> EngineOptimizer   : flat HBM layout, norm (K1) + fused step (K2/K3)
+    prepare(LRScheduler) -> EngineScheduler
+    accumulate / autocast / backward           : accumulation phase, bucketed all-reduce (K6)
+    scalar_accumulator / argmax_count          : device-side Meter and loss bookkeeping (K4)
+
+One process per GPU; ``torch.distributed`` (NCCL over NVLink) is initialised from the usual
+RANK / WORLD_SIZE / LOCAL_RANK / MASTER_* environment when WORLD_SIZE > 1.
+"""
+from __future__ import annotations
+
+import contextlib
+import os
+import pickle
+
+import torch
+import torch.distributed as dist
+
+from rocket_b200 import tracking
+from rocket_b200.comm import BufferSync, GradSync, broadcast_module_state
+from rocket_b200.deferred import DeferredScalar
+from rocket_b200.flat import EngineOptimizer
+from rocket_b200.staging import EngineDataLoader, PinnedRingStager
+
+
+def _env_int(name: str, default: int) -> int:
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class EngineScheduler:
+    """Role of accelerate's AcceleratedScheduler (reference rocket/core/scheduler.py:92,113):
+    steps only on sync steps, ``world_size`` times, never past a OneCycle ``total_steps``."""
+
+    def __init__(self, scheduler, engine) -> None:
+        self.scheduler = scheduler
+        self.engine = engine
+
+    def step(self, *args, **kwargs) -> None:
+        eng = self.engine
+        if not eng.sync_gradients:
+            self.scheduler._step_count += 1     # accelerate's adjust_scheduler bookkeeping
+            return
+        if any(o.step_was_skipped for o in eng._optimizers):
+            return
+        for _ in range(eng.num_processes):
+            if hasattr(self.scheduler, "total_steps"):
+                if self.scheduler._step_count <= self.scheduler.total_steps:
+                    self.scheduler.step(*args, **kwargs)
+            else:
+                self.scheduler.step(*args, **kwargs)
+
+    def get_last_lr(self):
+        return self.scheduler.get_last_lr()
+
+    def state_dict(self):
+        return self.scheduler.state_dict()
+
+    def load_state_dict(self, state):
+        self.scheduler.load_state_dict(state)
+
+
+class ScalarAccumulator:
+    """Device-side running sum for the Loss capsule (reference rocket/core/loss.py:95-116)."""
+
+    _CHUNK = 1024
+
+    def __init__(self, engine, initial: float = 0.0) -> None:
+        self.engine = engine
+        self.acc = torch.full((1,), float(initial), dtype=torch.float64, device=engine.device)
+        self._ring = None
+        self._ring_pos = 0
+
+    def add(self, value: torch.Tensor, divisor: float) -> None:
+        self.engine.backend.scalar_accumulate(value.detach(), divisor, self.acc)
+
+    def _slot(self) -> torch.Tensor:
+        if self._ring is None or self._ring_pos == self._CHUNK:
+            ring = torch.empty(self._CHUNK, dtype=torch.float64)
+            self._ring = ring.pin_memory() if self.engine.device.type == "cuda" else ring
+            self._ring_pos = 0
+        slot = self._ring[self._ring_pos:self._ring_pos + 1]
+        self._ring_pos += 1
+        return slot
+
+    def publish_and_reset(self) -> DeferredScalar:
+        eng = self.engine
+        out = self.acc.clone()
+        self.acc.zero_()
+        if eng.num_processes > 1:                 # mean over ranks, as gather(loss).mean()
+            dist.all_reduce(out, op=dist.ReduceOp.SUM)
+            out /= eng.num_processes
+        slot = self._slot()
+        slot.copy_(out, non_blocking=True)
+        event = None
+        if eng.device.type == "cuda":
+            event = torch.cuda.Event()
+            event.record()
+        return DeferredScalar(slot, event)
+
+    def peek(self) -> float:
+        return float(self.acc.item())
+
+
+class Engine:
+    def __init__(self, device_placement: bool = True, mixed_precision: str | None = None,
+                 gradient_accumulation_steps: int = 1, project_config=None,
+                 project_dir: str | None = None, *, backend=None, device=None,
+                 stage_slots: int = 3, stage_threads: int = 4, bucket_cap_mb: float = 32.0,
+                 stage_batches: bool = True) -> None:
+        world = _env_int("WORLD_SIZE", 1)
+        self.local_process_index = _env_int("LOCAL_RANK", 0)
+        if device is None:
+            if torch.cuda.is_available():
+                device = torch.device("cuda", self.local_process_index)
+            elif backend is not None:
+                device = torch.device("cpu")      # host-only test double
+            else:
+                raise RuntimeError(
+                    "rocket_b200 runs on CUDA (B200, sm_100a) only: no CUDA device is "
+                    "available and there is no CPU fallback.")
+        self.device = torch.device(device)
+        if self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
+        if world > 1 and not dist.is_initialized():
+            if self.device.type == "cuda":
+                dist.init_process_group("nccl", device_id=self.device)
+            else:
+                dist.init_process_group("gloo")
+        self._owns_pg = world > 1
+        if dist.is_available() and dist.is_initialized():
+            self.process_index, self.num_processes = dist.get_rank(), dist.get_world_size()
+        else:
+            self.process_index, self.num_processes = 0, 1
+        if backend is None:
+            from rocket_b200.backend import NativeBackend
+            backend = NativeBackend(self.device)
+        self.backend = backend
+        self.device_placement = device_placement
+        self.mixed_precision = mixed_precision if mixed_precision not in (None, "no") else "no"
+        if self.mixed_precision == "fp16":
+            raise NotImplementedError("mixed_precision='fp16' (GradScaler) is not implemented; "
+                                      "use 'bf16'")
+        if self.mixed_precision not in ("no", "bf16"):
+            raise ValueError(f"unknown mixed_precision {mixed_precision!r}")
+        self._accum_steps = int(gradient_accumulation_steps)
+        self.sync_gradients = True
+        self.step = 0
+        self.project_dir = project_dir if project_dir is not None else \
+            getattr(project_config, "project_dir", None)
+        self._models, self._optimizers, self._schedulers = [], [], []
+        self._dataloaders, self._custom_objects = [], []
+        self.log_with: list = []
+        self.trackers: list = []
+        self._active_dataloaders: list = []
+        self._grad_sync: dict = {}
+        self._buffer_sync: list = []
+        self._bucket_cap_mb = bucket_cap_mb
+        self.stager = None
+        if self.device.type == "cuda" and stage_batches:
+            self.stager = PinnedRingStager(self.device, slots=stage_slots,
+                                           copy_threads=stage_threads)
+
+    # ---- plain attributes the capsules read -----------------------------------------------------
+    @property
+    def gradient_accumulation_steps(self) -> int:
+        return self._accum_steps
+
+    @property
+    def is_main_process(self) -> bool:
+        return self.process_index == 0
+
+    @property
+    def is_local_main_process(self) -> bool:
+        return self.local_process_index == 0
+
+    # ---- prepare (reference dataset.py:178, module.py:106, optimizer.py:109, scheduler.py:92) ----
+    def prepare(self, *objects, device_placement=None):
+        out = tuple(self._prepare_one(o) for o in objects)
+        return out[0] if len(out) == 1 else out
+
+    def _prepare_one(self, obj):
+        if isinstance(obj, torch.utils.data.DataLoader):
+            loader = EngineDataLoader(obj, self)
+            self._dataloaders.append(loader)
+            return loader
+        if isinstance(obj, torch.nn.Module):
+            return self._prepare_model(obj)
+        if isinstance(obj, torch.optim.Optimizer):
+            opt = EngineOptimizer(obj, self)
+            if self.num_processes > 1:
+                self._grad_sync[id(opt)] = GradSync(opt, self, self._bucket_cap_mb)
+            self._optimizers.append(opt)
+            return opt
+        if isinstance(obj, torch.optim.lr_scheduler.LRScheduler):
+            sched = EngineScheduler(obj, self)
+            self._schedulers.append(sched)
+            return sched
+        return obj
+
+    def _prepare_model(self, model: torch.nn.Module) -> torch.nn.Module:
+        if self.num_processes > 1:
+            broadcast_module_state(model, src=0)
+            if any(True for _ in model.buffers()):
+                self._buffer_sync.append(BufferSync(model))
+        if self.mixed_precision == "bf16" and not getattr(model, "_rk_autocast", False):
+            inner = model.forward
+            dev_type = self.device.type
+
+            def forward(*args, **kwargs):
+                with torch.autocast(device_type=dev_type, dtype=torch.bfloat16):
+                    out = inner(*args, **kwargs)
+                return _to_fp32(out)
+
+            model.forward = forward
+            model._rk_autocast = True
+        self._models.append(model)
+        return model
+
+    def skip_first_batches(self, dataloader, num_batches: int = 0):
+        """reference dataset.py:206-208: loader that skips the first batches (resume)."""
+        return EngineDataLoader(dataloader.base, self,
+                                skip_batches=dataloader.skip_batches + num_batches)
+
+    # ---- step contexts (reference module.py:210-211) ------------------------------------------------
+    def _begin_dataloader(self, loader) -> None:
+        self._active_dataloaders.append(loader)
+
+    def _end_dataloader(self, loader) -> None:
+        if loader in self._active_dataloaders:
+            self._active_dataloaders.remove(loader)
+
+    @property
+    def end_of_dataloader(self) -> bool:
+        return bool(self._active_dataloaders) and self._active_dataloaders[-1].end_of_dataloader
+
+    @property
+    def remainder(self) -> int:
+        return self._active_dataloaders[-1].remainder if self._active_dataloaders else -1
+
+    @contextlib.contextmanager
+    def accumulate(self, *models):
+        """Advance the accumulation phase: every N-th call, and always on the last batch of
+        the active loader, is a gradient-sync step [accelerate ``_do_sync``, from memory]."""
+        if self.end_of_dataloader:
+            self.step = 0
+            self.sync_gradients = True
+        else:
+            self.step += 1
+            self.sync_gradients = (self.step % self._accum_steps) == 0
+        yield
+
+    @contextlib.contextmanager
+    def autocast(self, autocast_handler=None):
+        if self.mixed_precision == "bf16":
+            with torch.autocast(device_type=self.device.type, dtype=torch.bfloat16):
+                yield
+        else:
+            yield
+
+    def backward(self, loss: torch.Tensor, **kwargs) -> None:
+        """reference loss.py:119: scale by 1/accumulation_steps, then autograd.  Bucketed
+        all-reduces start from gradient hooks while this runs (sync steps only)."""
+        (loss / self._accum_steps).backward(**kwargs)
+
+    # ---- gradient exchange -----------------------------------------------------------------------------
+    def grad_scale(self) -> float:
+        """Factor the kernels apply when they read a gradient: 1/world_size, because the
+        wire reduction is a plain SUM."""
+        return 1.0 / self.num_processes
+
+    def finish_grad_sync(self, opt) -> None:
+        sync = self._grad_sync.get(id(opt))
+        if sync is not None:
+            sync.finish()
+
+    def note_late_gradient(self, opt) -> None:
+        """A gradient was adopted into the flat buffer after backward: its bucket has not
+        been reduced by a hook; GradSync.finish() launches it."""
+        return None
+
+    def clip_grad_norm_(self, parameters=None, max_norm: float = 1.0, norm_type: float = 2.0):
+        """Global-norm clipping for user capsules (accelerate: ``clip_grad_norm_``).  The
+        coefficient is applied inside the next fused step; returns the device norm."""
+        if float(norm_type) != 2.0:
+            raise NotImplementedError("only the L2 norm is implemented")
+        if not self.sync_gradients:
+            return None
+        norms = []
+        for opt in self._optimizers:
+            self.finish_grad_sync(opt)
+            norms.append(opt.clip_grad_norm_(max_norm))
+        if len(norms) != 1:
+            raise NotImplementedError("clip_grad_norm_ with several optimizers: set "
+                                      "max_grad_norm on each Optimizer capsule instead")
+        return norms[0]
+
+    # ---- collectives the capsules call (reference loss.py:95, meter.py:93) ----------------------------------
+    def gather(self, tensor):
+        if self.num_processes == 1:
+            return tensor
+        return _recursively(self._gather_one, tensor)
+
+    def _gather_one(self, t: torch.Tensor) -> torch.Tensor:
+        t = t.detach()
+        if t.ndim == 0:
+            t = t[None]
+        t = t.contiguous()
+        out = torch.empty((self.num_processes * t.shape[0],) + tuple(t.shape[1:]),
+                          dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t) if t.device.type == "cuda" else \
+            dist.all_gather(list(out.chunk(self.num_processes)), t)
+        return out
+
+    def gather_for_metrics(self, input_data):
+        data = self.gather(input_data)
+        if self.num_processes > 1 and self.end_of_dataloader and self.remainder > 0:
+            rem = self.remainder
+            return _recursively(lambda t: t[:rem], data)
+        return data
+
+    def valid_rows(self, n_rows: int) -> int:
+        """How many of this rank's ``n_rows`` samples in the current batch are real (not
+        ``even_batches`` padding): the local view of gather_for_metrics' truncation."""
+        if self.num_processes == 1 or not self.end_of_dataloader or self.remainder <= 0:
+            return n_rows
+        lo = self.process_index * n_rows
+        return max(0, min(n_rows, self.remainder - lo))
+
+    def broadcast_object_list(self, object_list, from_process: int = 0):
+        if self.num_processes > 1:
+            dist.broadcast_object_list(object_list, src=from_process)
+        return object_list
+
+    def wait_for_everyone(self) -> None:
+        if self.num_processes > 1:
+            dist.barrier()
+
+    # ---- device-side Meter / loss bookkeeping ---------------------------------------------------------------
+    def scalar_accumulator(self, initial: float = 0.0) -> ScalarAccumulator:
+        return ScalarAccumulator(self, initial)
+
+    def new_counters(self, n: int = 2) -> torch.Tensor:
+        return torch.zeros(n, dtype=torch.int64, device=self.device)
+
+    def argmax_count(self, logits, labels, counters) -> None:
+        self.backend.argmax_count(logits, labels, counters)
+
+    def read_counters(self, counters: torch.Tensor, reduce: bool = True) -> DeferredScalar:
+        """Async copy of integer counters to the host (summed over ranks when ``reduce``)."""
+        out = counters.clone()
+        if reduce and self.num_processes > 1:
+            dist.all_reduce(out, op=dist.ReduceOp.SUM)
+        host = torch.empty(out.shape, dtype=out.dtype)
+        event = None
+        if self.device.type == "cuda":
+            host = host.pin_memory()
+            host.copy_(out, non_blocking=True)
+            event = torch.cuda.Event()
+            event.record()
+        else:
+            host.copy_(out)
+        return DeferredScalar(host, event)
+
+    # ---- checkpointing (reference capsule.py:139, checkpoint.py:129, launcher.py:356-363) ----------------------
+    def register_for_checkpointing(self, *objects) -> None:
+        bad = [o for o in objects
+               if not (hasattr(o, "state_dict") and hasattr(o, "load_state_dict"))]
+        if bad:
+            raise ValueError("objects registered for checkpointing need state_dict() and "
+                             f"load_state_dict(): {[type(o).__name__ for o in bad]}")
+        self._custom_objects.extend(objects)
+
+    def save_state(self, output_dir: str | None = None, **_) -> str:
+        if output_dir is None:
+            if self.project_dir is None:
+                raise ValueError("save_state needs an output_dir or a project_dir")
+            output_dir = os.path.join(self.project_dir, "checkpoints")
+        states = {
+            "models": [m.state_dict() for m in self._models],
+            "optimizers": [o.state_dict() for o in self._optimizers],
+            "schedulers": [s.state_dict() for s in self._schedulers],
+            "custom": [c.state_dict() for c in self._custom_objects],
+        }
+        if self.is_main_process:
+            os.makedirs(output_dir, exist_ok=True)
+            for i, sd in enumerate(states["models"]):
+                torch.save(sd, os.path.join(output_dir, f"model_{i}.pt"))
+            for i, sd in enumerate(states["optimizers"]):
+                torch.save(sd, os.path.join(output_dir, f"optimizer_{i}.pt"))
+            for i, sd in enumerate(states["schedulers"]):
+                torch.save(sd, os.path.join(output_dir, f"scheduler_{i}.pt"))
+            for i, sd in enumerate(states["custom"]):
+                with open(os.path.join(output_dir, f"custom_checkpoint_{i}.pkl"), "wb") as f:
+                    pickle.dump(sd, f)
+        os.makedirs(output_dir, exist_ok=True)
+        rng = {"torch": torch.get_rng_state()}
+        if self.device.type == "cuda":
+            rng["cuda"] = torch.cuda.get_rng_state(self.device)
+        torch.save(rng, os.path.join(output_dir, f"random_states_{self.process_index}.pt"))
+        self.wait_for_everyone()
+        return output_dir
+
+    def load_state(self, input_dir: str | None = None, **_) -> None:
+        if input_dir is None or not os.path.isdir(input_dir):
+            raise RuntimeError(f"checkpoint directory {input_dir!r} does not exist")
+        dev = self.device
+        for i, m in enumerate(self._models):
+            m.load_state_dict(torch.load(os.path.join(input_dir, f"model_{i}.pt"),
+                                         map_location=dev))
+        for i, o in enumerate(self._optimizers):
+            o.load_state_dict(torch.load(os.path.join(input_dir, f"optimizer_{i}.pt"),
+                                         map_location=dev))
+        for i, s in enumerate(self._schedulers):
+            s.load_state_dict(torch.load(os.path.join(input_dir, f"scheduler_{i}.pt")))
+        for i, c in enumerate(self._custom_objects):
+            with open(os.path.join(input_dir, f"custom_checkpoint_{i}.pkl"), "rb") as f:
+                c.load_state_dict(pickle.load(f))
+        rng_path = os.path.join(input_dir, f"random_states_{self.process_index}.pt")
+        if os.path.exists(rng_path):
+            rng = torch.load(rng_path)
+            torch.set_rng_state(rng["torch"])
+            if "cuda" in rng and dev.type == "cuda":
+                torch.cuda.set_rng_state(rng["cuda"], dev)
+
+    # ---- trackers (reference tracker.py:89-105) -----------------------------------------------------------------
+    def get_tracker(self, name: str, unwrap: bool = False):
+        for t in self.trackers:
+            if t.name == name:
+                return t
+        return tracking.GeneralTracker()
+
+    def init_trackers(self, project_name: str, config: dict | None = None, init_kwargs=None):
+        for name in self.log_with:
+            if any(t.name == name for t in self.trackers):
+                continue
+            if isinstance(name, tracking.GeneralTracker):
+                self.trackers.append(name)
+            else:
+                self.trackers.append(
+                    tracking.make_tracker(name, project_name, self.project_dir))
+
+    def end_training(self) -> None:
+        for t in self.trackers:
+            t.finish()
+        for sync in self._grad_sync.values():
+            sync.remove()
+        self._grad_sync.clear()
+        for b in self._buffer_sync:
+            b.remove()
+        self._buffer_sync.clear()
+        if self.stager is not None:
+            self.stager.close()
+
+    def destroy_process_group(self) -> None:
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def _recursively(fn, data):
+    if isinstance(data, torch.Tensor):
+        return fn(data)
+    if isinstance(data, dict):
+        return type(data)({k: _recursively(fn, v) for k, v in data.items()})
+    if isinstance(data, tuple) and hasattr(data, "_fields"):
+        return type(data)(*[_recursively(fn, v) for v in data])
+    if isinstance(data, (list, tuple)):
+        return type(data)(_recursively(fn, v) for v in data)
+    return data
+
+
+def _to_fp32(data):
+    return _recursively(
+        lambda t: t.float() if t.dtype in (torch.bfloat16, torch.float16) else t, data)
+
+
+def notebook_launcher(function, args=(), num_processes=None, num_nodes=1, **_):
+    """Jupyter entry (reference launcher.py:238-244).  Single process: call through;
+    multi-process spawning from a notebook is not part of the hot path."""
+    if num_processes not in (None, 1):
+        raise NotImplementedError("use torchrun for multi-process runs")
+    function(*args)

@@ -1,0 +1,288 @@
+"""Prepared optimizer: flat HBM layout + the fused step.
+
+What ``Engine.prepare(optimizer)`` returns.  It plays the role of accelerate's
+``AcceleratedOptimizer`` for the reference's Optimizer capsule (reference
+rocket/core/optimizer.py:92-109,129-130,138): ``.optimizer``, ``.param_groups``, ``.step()``
+and ``.zero_grad()``, the last two being no-ops on gradient-accumulation steps.
+
+HBM layout (built once): every trainable parameter of every param group is re-homed into
+one flat fp32 buffer ``flat_p`` at a 256-byte aligned offset, and ``flat_g`` / ``flat_m`` /
+``flat_v`` mirror it.  ``param.data``, ``param.grad`` and the optimizer's
+``state[p]["exp_avg"]`` ... are views into those buffers, so user code, ``state_dict()`` and
+checkpoints see ordinary per-parameter tensors while the kernels see four aligned streams
+and the gradient all-reduce sees contiguous buckets (no copy-in / copy-out).
+
+Gradients stay allocated: the fused kernel zero-fills them, which is the in-place form of
+``zero_grad()``.  (The reference's ``zero_grad`` frees them, ``set_to_none=True``; code
+that tests ``p.grad is None`` after a step sees the difference.)  Parameters that have never
+received a gradient are skipped, as torch.optim skips ``grad is None``.
+"""
+from __future__ import annotations
+
+import torch
+
+from rocket_b200.backend import TensorSpec
+
+_ALIGN = 64  # elements: 256-byte aligned segment starts
+
+
+def _align(n: int) -> int:
+    return (n + _ALIGN - 1) // _ALIGN * _ALIGN
+
+
+class EngineOptimizer:
+    def __init__(self, optimizer: torch.optim.Optimizer, engine) -> None:
+        self.optimizer = optimizer
+        self.engine = engine
+        self.max_grad_norm: float | None = None
+        self.last_grad_norm: torch.Tensor | None = None   # device scalar, for logging
+        self._zeroed_by_step = False
+        self._pending_clip: float | None = None
+        self._kind = self._classify(optimizer)
+        self._build()
+
+    # ---- construction --------------------------------------------------------------------
+    @staticmethod
+    def _classify(opt) -> str:
+        kind = {torch.optim.AdamW: "adamw", torch.optim.Adam: "adam",
+                torch.optim.SGD: "sgd"}.get(type(opt))
+        if kind is None:
+            raise NotImplementedError(
+                f"rocket_b200 fuses torch.optim.AdamW, Adam and SGD; got {type(opt).__name__}. "
+                "There is no unfused fallback path.")
+        for group in opt.param_groups:
+            for flag in ("amsgrad", "maximize", "capturable", "differentiable"):
+                if group.get(flag):
+                    raise NotImplementedError(f"{type(opt).__name__}({flag}=True) is not supported")
+            if isinstance(group["lr"], torch.Tensor):
+                raise NotImplementedError("tensor learning rates are not supported")
+        if len(opt.param_groups) > 64:
+            raise NotImplementedError("at most 64 param groups (RK_MAX_GROUPS)")
+        return kind
+
+    def _build(self) -> None:
+        dev = self.engine.device
+        self._params: list[torch.nn.Parameter] = []
+        self._group_of: list[int] = []
+        self._offsets: list[int] = []
+        off = 0
+        for gi, group in enumerate(self.optimizer.param_groups):
+            for p in group["params"]:
+                if not p.requires_grad:
+                    continue
+                if p.dtype != torch.float32:
+                    raise NotImplementedError(
+                        f"parameters must be fp32 (master weights); got {p.dtype}")
+                if p.device != dev:
+                    raise RuntimeError(
+                        f"parameter on {p.device}, engine on {dev}: prepare the module first")
+                self._params.append(p)
+                self._group_of.append(gi)
+                self._offsets.append(off)
+                off += _align(p.numel())
+        if not self._params:
+            raise ValueError("optimizer has no trainable parameters")
+        self._total = off
+        self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(off, dtype=torch.float32, device=dev)
+        self._needs_m = self._kind != "sgd" or any(
+            g.get("momentum", 0) != 0 for g in self.optimizer.param_groups)
+        self.flat_m = torch.zeros(off, dtype=torch.float32, device=dev) if self._needs_m else None
+        self.flat_v = torch.zeros(off, dtype=torch.float32, device=dev) \
+            if self._kind != "sgd" else None
+        self._views_p, self._views_g, self._views_m, self._views_v = [], [], [], []
+        with torch.no_grad():
+            for p, o in zip(self._params, self._offsets):
+                n = p.numel()
+                vp = self.flat_p[o:o + n].view(p.shape)
+                vp.copy_(p.data)
+                p.data = vp
+                self._views_p.append(vp)
+                self._views_g.append(self.flat_g[o:o + n].view(p.shape))
+                self._views_m.append(self.flat_m[o:o + n].view(p.shape) if self._needs_m else None)
+                self._views_v.append(self.flat_v[o:o + n].view(p.shape)
+                                     if self.flat_v is not None else None)
+        self._grad_ptr = [v.data_ptr() for v in self._views_g]
+        self._adopted = [False] * len(self._params)      # grad lives in flat_g
+        self._group_step = [0] * len(self.optimizer.param_groups)
+        self._import_state()
+        self._plan = None
+        self._plan_skip = None
+
+    def _import_state(self) -> None:
+        """Adopt state the wrapped optimizer already holds (resume / prior training)."""
+        for i, p in enumerate(self._params):
+            st = self.optimizer.state.get(p)
+            if not st:
+                continue
+            gi = self._group_of[i]
+            if "step" in st:
+                self._group_step[gi] = max(self._group_step[gi], int(float(st["step"])))
+            if self._kind == "sgd":
+                buf = st.get("momentum_buffer")
+                if buf is not None and self._needs_m:
+                    self._views_m[i].copy_(buf)
+                    st["momentum_buffer"] = self._views_m[i]
+                    self._group_step[gi] = max(self._group_step[gi], 1)
+            else:
+                if "exp_avg" in st:
+                    self._views_m[i].copy_(st["exp_avg"])
+                    self._views_v[i].copy_(st["exp_avg_sq"])
+                    st["exp_avg"], st["exp_avg_sq"] = self._views_m[i], self._views_v[i]
+
+    # ---- the AcceleratedOptimizer surface ---------------------------------------------------
+    @property
+    def param_groups(self):
+        return self.optimizer.param_groups
+
+    @property
+    def state(self):
+        self._export_state()
+        return self.optimizer.state
+
+    @property
+    def step_was_skipped(self) -> bool:
+        return False
+
+    def zero_grad(self, set_to_none: bool | None = None) -> None:
+        if not self.engine.sync_gradients:
+            return
+        if self._zeroed_by_step:       # the fused step already cleared flat_g
+            self._zeroed_by_step = False
+            return
+        self.flat_g.zero_()
+        if set_to_none:
+            for i, p in enumerate(self._params):
+                if not self._adopted[i]:
+                    p.grad = None
+
+    def clip_grad_norm_(self, max_norm: float) -> torch.Tensor:
+        """Engine-level ``clip_grad_norm_``: computes the global norm now (one kernel) and
+        applies the coefficient inside the next fused step.  Returns the device norm."""
+        self._adopt_grads()
+        norm = self.engine.backend.l2norm(self._get_plan(), self.engine.grad_scale())
+        self._pending_clip = float(max_norm)
+        self.last_grad_norm = norm
+        return norm
+
+    def step(self, closure=None) -> None:
+        if closure is not None:
+            raise NotImplementedError("closures are not supported by the fused step")
+        eng = self.engine
+        if not eng.sync_gradients:
+            return
+        self._adopt_grads()
+        eng.finish_grad_sync(self)
+        plan = self._get_plan()
+        scale = eng.grad_scale()
+        max_norm = self._pending_clip if self._pending_clip is not None else self.max_grad_norm
+        norm = None
+        if max_norm is not None:
+            norm = self.last_grad_norm if self._pending_clip is not None \
+                else eng.backend.l2norm(plan, scale)
+            self.last_grad_norm = norm
+        self._pending_clip = None
+        active = set(self._group_of[i] for i in range(len(self._params)) if self._adopted[i])
+        groups = []
+        for gi, g in enumerate(self.optimizer.param_groups):
+            skip = gi not in active
+            if not skip:
+                self._group_step[gi] += 1
+            if self._kind == "sgd":
+                groups.append(dict(lr=float(g["lr"]), momentum=float(g["momentum"]),
+                                   dampening=float(g["dampening"]),
+                                   weight_decay=float(g["weight_decay"]),
+                                   nesterov=bool(g["nesterov"]),
+                                   first_step=self._group_step[gi] <= 1, skip=skip))
+            else:
+                groups.append(dict(lr=float(g["lr"]), beta1=float(g["betas"][0]),
+                                   beta2=float(g["betas"][1]), eps=float(g["eps"]),
+                                   weight_decay=float(g["weight_decay"]),
+                                   step=max(self._group_step[gi], 1),
+                                   decoupled=self._kind == "adamw"
+                                   or bool(g.get("decoupled_weight_decay", False)),
+                                   skip=skip))
+        fn = eng.backend.sgd_step if self._kind == "sgd" else eng.backend.adam_step
+        fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)
+        self._zeroed_by_step = True
+        self._state_dirty = True
+
+    # ---- gradient adoption -----------------------------------------------------------------------
+    def _adopt_grads(self) -> None:
+        """Make sure every gradient that exists lives in ``flat_g``.
+
+        Steady state: one pointer compare per parameter.  First sync step (or whenever user
+        code replaced ``p.grad``): copy the gradient into its flat view and re-point
+        ``p.grad`` there, so later backward passes accumulate in place.
+        """
+        changed = False
+        for i, p in enumerate(self._params):
+            g = p.grad
+            if g is None:
+                if self._adopted[i]:
+                    # user set it to None: treat as zero gradient, keep the slot
+                    self._views_g[i].zero_()
+                    p.grad = self._views_g[i]
+                continue
+            if g.data_ptr() != self._grad_ptr[i]:
+                if g.is_sparse:
+                    raise NotImplementedError("sparse gradients are not supported")
+                self._views_g[i].copy_(g)
+                p.grad = self._views_g[i]
+                self.engine.note_late_gradient(self)
+            if not self._adopted[i]:
+                self._adopted[i] = True
+                changed = True
+        if changed:
+            self._plan = None
+
+    def _get_plan(self):
+        if self._plan is None:
+            specs = [TensorSpec(p=self._views_p[i].reshape(-1), g=self._views_g[i].reshape(-1),
+                                m=self._views_m[i].reshape(-1) if self._needs_m else None,
+                                v=self._views_v[i].reshape(-1) if self.flat_v is not None else None,
+                                group=self._group_of[i], skip=not self._adopted[i])
+                     for i in range(len(self._params))]
+            self._plan = self.engine.backend.make_plan(specs)
+        return self._plan
+
+    # ---- state in torch's own format (checkpoints) ----------------------------------------------------
+    _state_dirty = False
+
+    def _export_state(self) -> None:
+        for i, p in enumerate(self._params):
+            if not self._adopted[i]:
+                continue
+            step = self._group_step[self._group_of[i]]
+            if step == 0:
+                continue
+            st = self.optimizer.state[p]
+            if self._kind == "sgd":
+                st["momentum_buffer"] = self._views_m[i] if self._needs_m else None
+            else:
+                st["step"] = torch.tensor(float(step), dtype=torch.float32)
+                st["exp_avg"], st["exp_avg_sq"] = self._views_m[i], self._views_v[i]
+        self._state_dirty = False
+
+    def state_dict(self) -> dict:
+        self._export_state()
+        return self.optimizer.state_dict()
+
+    def load_state_dict(self, state_dict: dict) -> None:
+        self.optimizer.load_state_dict(state_dict)
+        self._group_step = [0] * len(self.optimizer.param_groups)
+        with torch.no_grad():
+            self._import_state()
+            for i, p in enumerate(self._params):
+                if self.optimizer.state.get(p):
+                    if not self._adopted[i]:
+                        self._adopted[i] = True
+                        if p.grad is None or p.grad.data_ptr() != self._grad_ptr[i]:
+                            self._views_g[i].zero_()
+                            p.grad = self._views_g[i]
+                        self._plan = None
+
+    # ---- introspection used by bench / tests ---------------------------------------------------------------
+    @property
+    def numel(self) -> int:
+        return sum(p.numel() for p in self._params)

@@ -1,0 +1,317 @@
+"""Batch delivery: rank sharding + pinned-ring staging (kernel row K5).
+
+``EngineDataLoader`` is what ``Engine.prepare(DataLoader)`` returns (the reference calls it
+at rocket/core/dataset.py:178-180 and iterates the result at :267).  It restates the parts of
+accelerate's ``BatchSamplerShard`` / ``DataLoaderShard`` the reference depends on [accelerate,
+from memory -- SURVEY.md Appendix A]:
+
+* rank r draws batches r, r+W, r+2W ... of the base sampler's order; the last incomplete
+  round is completed from the first samples (``even_batches``), at the index level, so no
+  rank ever loads another rank's samples;
+* ``end_of_dataloader`` is raised while the last batch is out (forces a gradient sync);
+* ``remainder`` tells ``gather_for_metrics`` how many gathered samples of the last round are
+  real.
+
+On a CUDA engine each batch additionally goes through the native stager
+(``rk_stage_*`` in librocket_b200.so): a worker thread packs all tensor leaves of the batch
+into one pinned slot and issues a single async H2D copy on a side stream, one batch ahead of
+the consumer; the batch the capsules receive is a set of views into the device slot, ordered
+against the compute stream by events only.  A batch stays valid until ``slots - 1`` further
+batches have been drawn (the Looper drops ``attrs.batch`` every iteration).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Any
+
+import torch
+import torch.utils.data as tud
+
+from rocket_b200 import _native as N
+
+_SEG_ALIGN = 256
+
+
+# ---- index-level sharding ---------------------------------------------------------------------
+class ShardedBatchSampler(tud.Sampler):
+    """Rank-sharded view of a batch sampler with ``even_batches`` completion."""
+
+    def __init__(self, batch_sampler, world: int, rank: int):
+        self.batch_sampler = batch_sampler
+        self.world, self.rank = world, rank
+        self.batch_size = getattr(batch_sampler, "batch_size", None)
+        self.drop_last = getattr(batch_sampler, "drop_last", False)
+
+    def __len__(self) -> int:
+        n = len(self.batch_sampler)
+        if self.drop_last:
+            return n // self.world
+        return -(-n // self.world)
+
+    def __iter__(self):
+        W, rank, bs = self.world, self.rank, self.batch_size
+        head: list[int] = []          # samples of the first round, for the wrap-around
+        mine: list[int] = []
+        idx, batch = -1, []
+        for idx, batch in enumerate(self.batch_sampler):
+            batch = list(batch)
+            if not self.drop_last and idx < W:
+                head += batch
+            if idx % W == rank:
+                mine = batch
+            if idx % W == W - 1 and (bs is None or len(batch) == bs):
+                yield mine            # the round is complete and full-sized
+                mine = []
+        if self.drop_last or not head:
+            return
+        # incomplete last round and/or short last batch
+        if len(mine) == bs:
+            yield mine                # my batch of the last round was full: it is real
+        while len(head) < W * bs:
+            head += head
+        if len(batch) == bs:          # last batch seen was full: start a fresh one
+            batch = []
+            idx += 1
+        cursor = 0
+        while idx % W != 0 or len(batch) > 0:
+            end = cursor + bs - len(batch)
+            batch = batch + head[cursor:end]
+            if idx % W == rank:
+                yield batch
+            cursor = end
+            batch = []
+            idx += 1
+
+
+# ---- batch <-> flat segments ---------------------------------------------------------------------
+class _Leaf:
+    __slots__ = ("offset", "dtype", "shape", "nbytes")
+
+    def __init__(self, offset, dtype, shape, nbytes):
+        self.offset, self.dtype, self.shape, self.nbytes = offset, dtype, shape, nbytes
+
+
+def _flatten(batch, tensors: list) -> Any:
+    """Replace every CPU tensor leaf by a placeholder index; collect the tensors."""
+    if isinstance(batch, torch.Tensor):
+        if batch.device.type != "cpu" or batch.numel() == 0 or batch.is_sparse:
+            return batch
+        tensors.append(batch if batch.is_contiguous() else batch.contiguous())
+        return _Slot(len(tensors) - 1)
+    if isinstance(batch, dict):
+        return {k: _flatten(v, tensors) for k, v in batch.items()}
+    if isinstance(batch, tuple) and hasattr(batch, "_fields"):
+        return type(batch)(*[_flatten(v, tensors) for v in batch])
+    if isinstance(batch, (list, tuple)):
+        return type(batch)(_flatten(v, tensors) for v in batch)
+    return batch
+
+
+class _Slot:
+    __slots__ = ("i",)
+
+    def __init__(self, i):
+        self.i = i
+
+
+def _unflatten(template, leaves: list) -> Any:
+    if isinstance(template, _Slot):
+        return leaves[template.i]
+    if isinstance(template, dict):
+        return {k: _unflatten(v, leaves) for k, v in template.items()}
+    if isinstance(template, tuple) and hasattr(template, "_fields"):
+        return type(template)(*[_unflatten(v, leaves) for v in template])
+    if isinstance(template, (list, tuple)):
+        return type(template)(_unflatten(v, leaves) for v in template)
+    return template
+
+
+class PinnedRingStager:
+    """Python face of ``rk_stage_*``: owns the pinned and device rings (torch allocations,
+    passed to the library as raw pointers) and turns batches into device views."""
+
+    def __init__(self, device: torch.device, slots: int = 3, copy_threads: int = 4):
+        self.lib = N.load()
+        self.device = device
+        self.slots = slots
+        self.copy_threads = copy_threads
+        self.slot_bytes = 0
+        self._handle = None
+        self._pinned = self._dev = None
+        self._next = 0
+        self.h2d_bytes = 0
+        self.batches = 0
+
+    def _ensure(self, need: int) -> None:
+        if need <= self.slot_bytes:
+            return
+        self.close()
+        self.slot_bytes = max(1 << 20, -(-int(need * 1.25) // (1 << 20)) * (1 << 20))
+        total = self.slot_bytes * self.slots
+        self._pinned = torch.empty(total, dtype=torch.uint8).pin_memory()
+        self._dev = torch.empty(total, dtype=torch.uint8, device=self.device)
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            N.check(self.lib.rk_stage_create(ctypes.byref(handle), self._pinned.data_ptr(),
+                                             self._dev.data_ptr(), self.slot_bytes, self.slots,
+                                             self.copy_threads), "rk_stage_create")
+        self._handle = handle
+        self._next = 0
+
+    def submit(self, batch):
+        """Start staging ``batch``. Returns an opaque ticket for :meth:`collect`."""
+        tensors: list[torch.Tensor] = []
+        template = _flatten(batch, tensors)
+        if not tensors:
+            return (None, None, template, [], tensors)
+        leaves, off = [], 0
+        for t in tensors:
+            nbytes = t.numel() * t.element_size()
+            leaves.append(_Leaf(off, t.dtype, t.shape, nbytes))
+            off = -(-(off + nbytes) // _SEG_ALIGN) * _SEG_ALIGN
+        if off > self.slot_bytes:
+            torch.cuda.current_stream(self.device).synchronize()
+            self._ensure(off)
+        slot = self._next
+        self._next = (self._next + 1) % self.slots
+        n = len(tensors)
+        src = (ctypes.c_void_p * n)(*[t.data_ptr() for t in tensors])
+        offs = (ctypes.c_size_t * n)(*[lf.offset for lf in leaves])
+        sizes = (ctypes.c_size_t * n)(*[lf.nbytes for lf in leaves])
+        ticket = ctypes.c_uint64()
+        N.check(self.lib.rk_stage_submit(self._handle, slot, src, offs, sizes, n,
+                                         ctypes.byref(ticket)), "rk_stage_submit")
+        self.h2d_bytes += sum(lf.nbytes for lf in leaves)
+        self.batches += 1
+        # `tensors` is kept in the ticket so the host memory outlives the worker's memcpy
+        return (ticket.value, slot, template, leaves, tensors)
+
+    def collect(self, pending):
+        """Make the staged batch visible to the current stream and build the device views."""
+        ticket, slot, template, leaves, _keepalive = pending
+        if ticket is None:
+            return template, None
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.lib.rk_stage_wait(self._handle, ticket, stream), "rk_stage_wait")
+        base = slot * self.slot_bytes
+        out = []
+        for lf in leaves:
+            raw = self._dev[base + lf.offset: base + lf.offset + lf.nbytes]
+            out.append(raw.view(lf.dtype).view(lf.shape))
+        return _unflatten(template, out), slot
+
+    def release(self, slot) -> None:
+        if slot is None or self._handle is None:
+            return
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.lib.rk_stage_release(self._handle, slot, stream), "rk_stage_release")
+
+    def close(self) -> None:
+        if self._handle is not None:
+            torch.cuda.synchronize(self.device)
+            self.lib.rk_stage_destroy(self._handle)
+            self._handle = None
+        self._pinned = self._dev = None
+        self.slot_bytes = 0
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ---- the prepared loader -----------------------------------------------------------------------------
+class EngineDataLoader:
+    def __init__(self, base: tud.DataLoader, engine, skip_batches: int = 0):
+        self.base = base
+        self.engine = engine
+        self.skip_batches = skip_batches
+        self.dataset = base.dataset
+        self.batch_size = base.batch_size
+        self.end_of_dataloader = False
+        self.remainder = -1
+        self._loader = self._shard(base, engine.num_processes, engine.process_index)
+
+    @staticmethod
+    def _shard(base: tud.DataLoader, world: int, rank: int) -> tud.DataLoader:
+        if world == 1:
+            return base
+        if base.batch_sampler is None or isinstance(base.dataset, tud.IterableDataset):
+            raise NotImplementedError(
+                "multi-process runs need a map-style dataset with a batch sampler")
+        sharded = ShardedBatchSampler(base.batch_sampler, world, rank)
+        kwargs = dict(num_workers=base.num_workers, collate_fn=base.collate_fn,
+                      pin_memory=base.pin_memory, timeout=base.timeout,
+                      worker_init_fn=base.worker_init_fn, generator=base.generator,
+                      persistent_workers=base.persistent_workers)
+        if base.num_workers > 0:
+            kwargs["prefetch_factor"] = base.prefetch_factor
+            kwargs["multiprocessing_context"] = base.multiprocessing_context
+        return tud.DataLoader(base.dataset, batch_sampler=sharded, **kwargs)
+
+    def __len__(self) -> int:
+        return max(len(self._loader) - self.skip_batches, 0)
+
+    def _total_samples(self):
+        try:
+            return len(self.dataset)
+        except TypeError:
+            return None
+
+    def __iter__(self):
+        eng = self.engine
+        self.end_of_dataloader = False
+        total = self._total_samples()
+        if total is not None and self.batch_size:
+            self.remainder = total % (self.batch_size * eng.num_processes)
+        eng._begin_dataloader(self)
+        try:
+            yield from self._iterate()
+        finally:
+            eng._end_dataloader(self)
+
+    def _iterate(self):
+        stager = self.engine.stager
+        it = iter(self._loader)
+        try:
+            n_batches = len(self._loader)
+        except TypeError:
+            n_batches = None
+        for _ in range(self.skip_batches):
+            if next(it, None) is None:
+                return
+        index = self.skip_batches
+
+        def fetch():
+            data = next(it, None)
+            if data is None:
+                return None
+            return stager.submit(data) if stager is not None else data
+
+        pending = fetch()
+        held_slot = None
+        while pending is not None:
+            index += 1
+            if n_batches is not None:
+                nxt, have_next = None, index < n_batches
+            else:                                   # unsized loader: read ahead to see the end
+                nxt = fetch()
+                have_next = nxt is not None
+            if not have_next:
+                self.end_of_dataloader = True
+            if stager is not None:
+                batch, slot = stager.collect(pending)
+            else:
+                batch, slot = pending, None
+            yield batch
+            # the consumer has enqueued all work on this batch: its slot may be recycled
+            # once the compute stream gets here
+            if stager is not None:
+                stager.release(slot)
+            if n_batches is not None:
+                pending = fetch() if have_next else None
+            else:
+                pending = nxt
+            held_slot = slot
+        del held_slot
