@@ -1,0 +1,400 @@
+#!/usr/bin/env python
+"""bench.py -- rocket's per-iteration training step on B200: samples/sec + fused-step GB/s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): ResNet-18 (num_classes=10) on synthetic CIFAR-10-shaped
+3x32x32 batches, bs=256 per GPU, AdamW(lr=1e-3, wd=1e-2) + global-norm clip 1.0, fp32,
+driven through the unchanged capsule API (Launcher > Looper > Dataset/Module/Loss/
+Optimizer).  One "step" is one Looper iteration.
+
+Prints ONE JSON line (rank 0):
+  value     train samples/s, whole job, batch already resident in HBM when timing starts
+  e2e       same metric through the public API with HOST batches: pinned-ring H2D staging and
+            the loss read back to the host are inside the timed region
+  roofline  the fused AdamW step kernel: algorithmic 32 B/param / CUDA-event duration measured
+            live in the timed region, against MEASURED_PEAKS.json
+  optstep   config[4] microbench (fused norm+AdamW+zero over 1e9 fp32 params), same kernels
+  cpu_baseline  the looper port (torch.optim foreach=False) on this box's host cores,
+            bounded sample
+
+--impl reference times that CPU port alone, with all host threads (the reference itself is
+pure Python + torch and is not present on the GPU box; oracle/looper_port.py restates it).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+os.environ.setdefault("TQDM_DISABLE", "1")
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+BATCH = 256
+METRIC = "train samples/sec (ResNet-18 CIFAR-shaped bs=256/GPU, AdamW+clip) + fused-step HBM GB/s"
+ALGO_BYTES_STEP = 32      # AdamW update 28 B + grad zero-fill 4 B per fp32 param (K2)
+ALGO_BYTES_NORM = 4       # K1
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons, sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                     "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6
+                          for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+# ---- workload ----------------------------------------------------------------------------------
+def make_resnet18():
+    import torchvision
+    import workloads
+    torch.manual_seed(0)
+    return workloads.BatchModel(torchvision.models.resnet18(num_classes=10))
+
+
+def synthetic_batch(rank: int, n: int = BATCH):
+    g = torch.Generator().manual_seed(1234 + rank)
+    return torch.randn(n, 3, 32, 32, generator=g), torch.randint(0, 10, (n,), generator=g)
+
+
+def run_ours(args) -> dict:
+    import rocket_b200 as rk
+    import workloads
+    from rocket_b200 import _native
+    from rocket_b200.backend import NativeBackend
+    from rocket_b200.engine import Engine
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    W, K = args.warmup, args.steps
+    assert W >= 3, "timing rules: at least 3 warm-up steps"
+    torch.backends.cudnn.benchmark = True
+
+    class TimedBackend(NativeBackend):
+        """Brackets each engine kernel launch with CUDA events on its own stream."""
+        def __init__(self, device):
+            super().__init__(device)
+            self.timing = False
+            self.ev = {"norm": [], "step": []}
+
+        def _timed(self, key, fn, *a, **k):
+            if not self.timing:
+                return fn(*a, **k)
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            out = fn(*a, **k)
+            e.record()
+            self.ev[key].append((s, e))
+            return out
+
+        def l2norm(self, *a, **k):
+            return self._timed("norm", super().l2norm, *a, **k)
+
+        def adam_step(self, *a, **k):
+            return self._timed("step", super().adam_step, *a, **k)
+
+    holder = {}
+
+    def factory(**kw):
+        dev = torch.device("cuda", local)
+        torch.cuda.set_device(dev)
+        eng = Engine(backend=TimedBackend(dev), device=dev, **kw)
+        holder["engine"] = eng
+        return eng
+
+    rk.Launcher.engine_factory = staticmethod(factory)
+
+    class ResidentBatch(rk.Capsule):
+        """Hands the Looper one batch that already lives in HBM (the `value` leg)."""
+        def __init__(self, batch):
+            super().__init__(priority=2000)
+            self._host, self._dev = batch, None
+
+        def setup(self, attrs=None):
+            super().setup(attrs)
+            self._dev = [t.to(self._accelerator.device) for t in self._host]
+
+        def launch(self, attrs=None):
+            attrs.batch = list(self._dev)
+            attrs.looper.terminate = False
+
+    class Probe(rk.Capsule):
+        """Runs last in every iteration; opens the timed region after W steps and closes it
+        after W+K, with a barrier + device sync on both sides (CUDA events, device time)."""
+        def __init__(self, read_loss: bool):
+            super().__init__(priority=0)
+            self.i, self.read_loss = 0, read_loss
+            self.t0 = torch.cuda.Event(enable_timing=True)
+            self.t1 = torch.cuda.Event(enable_timing=True)
+            self.ms = self.launches = None
+            self.losses = []
+            self.sampler = ClockSampler(local)
+
+        def _fence(self):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+                torch.cuda.synchronize()
+
+        def launch(self, attrs=None):
+            self.i += 1
+            be = self._accelerator.backend
+            if self.i > W and self.read_loss and attrs.looper.state.loss is not None:
+                self.losses.append(attrs.looper.state.loss)
+            if self.i == W:
+                self._fence()
+                self.launch0 = _native.launch_count()
+                be.timing = True
+                if rank == 0:
+                    self.sampler.start()
+                self.t0.record()
+            elif self.i == W + K:
+                if self.read_loss:            # the host must hold every step's loss
+                    self.host_losses = [float(v) for v in self.losses]
+                self.t1.record()
+                self._fence()
+                be.timing = False
+                self.launches = _native.launch_count() - self.launch0
+                self.clocks = self.sampler.stop() if rank == 0 else None
+                self.ms = self.t0.elapsed_time(self.t1)
+
+    def graph(data_capsule, probe):
+        net = make_resnet18()
+        opt = torch.optim.AdamW(net.parameters(), lr=1e-3, weight_decay=1e-2)
+        inner = [rk.Loss(objective=workloads.CrossEntropy()),
+                 rk.Optimizer(opt, max_grad_norm=1.0)]
+        looper = rk.Looper([data_capsule, rk.Module(net, capsules=inner), probe],
+                           tag="bench", repeats=W + K)
+        return rk.Launcher([looper], num_epochs=1, destroy_process_group_after_launch=False), opt
+
+    # ---- leg 1: inputs resident in HBM -----------------------------------------------------------
+    probe = Probe(read_loss=False)
+    launcher, opt = graph(ResidentBatch(synthetic_batch(rank)), probe)
+    launcher.launch()
+    be = holder["engine"].backend
+    n_params = sum(p.numel() for p in opt.param_groups[0]["params"])
+    step_ms = [s.elapsed_time(e) for s, e in be.ev["step"]]
+    norm_ms = [s.elapsed_time(e) for s, e in be.ev["norm"]]
+    ms = torch.tensor([probe.ms], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    value = world * BATCH * K / (ms_total / 1e3)
+    launches, clocks = probe.launches, probe.clocks
+
+    # ---- leg 2: end to end, host batches through Dataset + stager ----------------------------------
+    class PoolDataset(torch.utils.data.Dataset):
+        """(W+K)*world batches of host samples drawn from a fixed synthetic pool."""
+        def __init__(self, pool: int, length: int):
+            g = torch.Generator().manual_seed(99)
+            self.x = torch.randn(pool, 3, 32, 32, generator=g)
+            self.y = torch.randint(0, 10, (pool,), generator=g)
+            self.length = length
+
+        def __len__(self):
+            return self.length
+
+        def __getitem__(self, i):
+            j = i % self.x.shape[0]
+            return self.x[j], self.y[j]
+
+    host_ds = PoolDataset(pool=16 * BATCH, length=(W + K) * BATCH * world)
+    probe2 = Probe(read_loss=True)
+    launcher2, _ = graph(rk.Dataset(host_ds, batch_size=BATCH, shuffle=False), probe2)
+    launcher2.launch()
+    ms2 = torch.tensor([probe2.ms], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+    e2e_value = world * BATCH * K / (float(ms2.item()) / 1e3)
+    h2d = BATCH * (3 * 32 * 32 * 4 + 8)
+
+    peak, peak_src = peaks()
+    k2_ms = statistics.mean(step_ms) if step_ms else float("nan")
+    achieved = ALGO_BYTES_STEP * n_params / (k2_ms * 1e-3) / 1e9
+    out = {
+        "metric": METRIC, "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": round(ms_total / K, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "configs[1]: ResNet-18(num_classes=10), synthetic 3x32x32, "
+                               "bs=256/GPU, AdamW(lr=1e-3,wd=1e-2)+clip 1.0, fp32, capsule API",
+                   "global_batch": BATCH * world, "parallelism": f"dp{world}",
+                   "l2": "no explicit flush: per-step working set (45 MB x4 optimizer streams "
+                         "+ activations of bs 256) exceeds the 126 MB L2",
+                   "params": n_params},
+        "e2e": {"value": round(e2e_value, 1), "unit": "samples/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+                "ms_per_step": round(float(ms2.item()) / K, 4)},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "rk_step_kernel<AdamOp> (fused AdamW+clip+zero)",
+                     "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(achieved / peak, 4), "traffic": None,
+                     "peak_source": peak_src, "algorithmic_bytes_per_param": ALGO_BYTES_STEP,
+                     "launch_ms": round(k2_ms, 5),
+                     "norm_kernel_ms": round(statistics.mean(norm_ms), 5) if norm_ms else None,
+                     "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
+    }
+    if rank == 0 and world == 1 and not args.no_optstep:
+        out["optstep"] = optstep_microbench(peak)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        out["cpu_baseline"] = cpu_port(budget_s=args.cpu_budget, threads=None, as_line=False)
+    return out
+
+
+def optstep_microbench(peak: float, n: int = 1_000_000_000, steps: int = 20, warmup: int = 5):
+    """configs[4]: fused norm + AdamW + clip + zero_grad over 1e9 fp32 params (one flat
+    tensor, 16 GB of state: far larger than L2), timed per kernel with CUDA events."""
+    from rocket_b200.backend import NativeBackend, TensorSpec
+    dev = torch.device("cuda", torch.cuda.current_device())
+    be = NativeBackend(dev)
+    p = torch.randn(n, device=dev) * 0.02
+    g = torch.empty(n, device=dev)
+    m = torch.zeros(n, device=dev)
+    v = torch.zeros(n, device=dev)
+    plan = be.make_plan([TensorSpec(p=p, g=g, m=m, v=v, group=0)])
+    hp = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2, decoupled=True)
+    tn, ts = [], []
+    for i in range(warmup + steps):
+        g.normal_(0, 1e-3)                                  # fresh grads: clipping is active
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
+        norm = be.l2norm(plan, 1.0)
+        e[1].record()
+        be.adam_step(plan, [dict(hp, step=i + 1)], norm, 1.0, 1.0, True)
+        e[2].record()
+        torch.cuda.synchronize()
+        if i >= warmup:
+            tn.append(e[0].elapsed_time(e[1]))
+            ts.append(e[1].elapsed_time(e[2]))
+    del p, g, m, v
+    torch.cuda.empty_cache()
+    t_norm, t_step = statistics.mean(tn), statistics.mean(ts)
+    gbs_step = ALGO_BYTES_STEP * n / (t_step * 1e-3) / 1e9
+    gbs_norm = ALGO_BYTES_NORM * n / (t_norm * 1e-3) / 1e9
+    gbs_full = (ALGO_BYTES_STEP + ALGO_BYTES_NORM) * n / ((t_step + t_norm) * 1e-3) / 1e9
+    return {"params": n, "layout": "one flat fp32 tensor", "steps": steps,
+            "step_kernel_ms": round(t_step, 4), "norm_kernel_ms": round(t_norm, 4),
+            "step_kernel_gbs": round(gbs_step, 1), "norm_kernel_gbs": round(gbs_norm, 1),
+            "full_step_gbs_36B": round(gbs_full, 1),
+            "frac_of_measured_peak": round(gbs_full / peak, 4),
+            "frac_of_nominal_8000": round(gbs_full / 8000.0, 4)}
+
+
+def cpu_port(budget_s: float, threads, as_line: bool, steps=None, warmup=1):
+    """The looper port on the host cores: ResNet-18 bs=256, AdamW(foreach=False) + clip."""
+    import workloads
+    from oracle import looper_port
+    if threads:
+        torch.set_num_threads(threads)
+    net = make_resnet18()
+    opt = torch.optim.AdamW(net.parameters(), lr=1e-3, weight_decay=1e-2, foreach=False)
+    batch = synthetic_batch(0)
+    obj = workloads.CrossEntropy()
+    if steps is None:                      # bounded sample: as many steps as fit the budget
+        t1 = looper_port.time_steps(net, obj, opt, batch, steps=1, warmup=1, max_norm=1.0,
+                                    device="cpu")
+        steps = max(3, min(50, int(budget_s / max(t1, 1e-3))))
+    sec = looper_port.time_steps(net, obj, opt, batch, steps=steps, warmup=warmup, max_norm=1.0,
+                                 device="cpu")
+    return {"value": round(BATCH / sec, 2), "unit": "samples/s", "cores": torch.get_num_threads(),
+            "kind": "port", "ms_per_step": round(sec * 1e3, 2),
+            "sample": f"{steps} steps of the same workload (ResNet-18 bs=256, fp32) on CPU, "
+                      f"os.cpu_count()={os.cpu_count()}"}
+
+
+def run_reference(args) -> dict:
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return {}
+    base = cpu_port(budget_s=0, threads=os.cpu_count(), as_line=True,
+                    steps=max(1, min(args.steps, 10)), warmup=max(1, min(args.warmup, 2)))
+    return {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": "samples/s",
+            "n_gpus": args.gpus, "steps": max(1, min(args.steps, 10)), "warmup": args.warmup,
+            "ms_per_step": base["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[1]: ResNet-18(num_classes=10), synthetic 3x32x32, "
+                                   "bs=256, AdamW+clip 1.0, fp32; reference arithmetic "
+                                   "(torch.optim foreach=False) on host CPU cores"},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": "samples/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0}}
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-optstep", action="store_true", help="skip the 1e9-param microbench")
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        out = run_reference(args)
+        if out:
+            print(json.dumps(out), flush=True)
+        return
+    out = run_ours(args)
+    if int(os.environ.get("RANK", 0)) == 0:
+        print(json.dumps(out), flush=True)
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

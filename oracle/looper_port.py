@@ -1,0 +1,154 @@
+"""looper_port.py -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+Pure-torch, single-process restatement ("port") of what one epoch of the reference's
+Looper does with the example graph, written as straight-line code with no capsules, no
+accelerate and no engine.  It is the oracle that can TRAVEL: /root/reference is not present
+on the GPU box, so GPU parity tests and bench.py's CPU baseline use this, after
+tests/test_oracle.py has pinned it (on CPU, in the build container) against golden vectors
+produced by the unmodified reference (tests/golden/make_golden.py).
+
+Order of operations per micro-batch, with the reference line each step restates:
+
+    batch = next(loader); move to device                  rocket/core/dataset.py:267-282
+    model.train(); forward                                 rocket/core/module.py:130-139
+    accumulate(): step counter / forced sync on last batch  module.py:211 (accelerate _do_sync)
+    loss = objective(batch)                                rocket/core/loss.py:92
+    value += loss.item() / accum                           loss.py:95-98
+    on sync: post (step, value); value = 0; step += 1      loss.py:101-116
+    (loss / accum).backward()                              loss.py:119 (accelerate.backward)
+    on sync: [clip_grad_norm_]; opt.step(); opt.zero_grad()  rocket/core/optimizer.py:129-130
+    on sync: post lr                                       optimizer.py:133-147
+    on sync: scheduler.step() x world_size                 rocket/core/scheduler.py:113
+    eval loop: forward in eval mode, argmax counts         rocket/core/meter.py:63-105,
+                                                           examples/mnist.py:26-34
+
+All arithmetic is torch's own (``torch.optim.*(foreach=False)``,
+``clip_grad_norm_(foreach=False)``), on whatever device is passed.
+"""
+from __future__ import annotations
+
+import time
+
+import torch
+
+
+def train_epoch(net, objective, opt, sched, batches, *, accum: int, max_norm, device,
+                state: dict, world: int = 1, sync_loss: bool = True) -> None:
+    """One pass over ``batches`` (a sized iterable of CPU batches). Appends to ``state``:
+    loss_steps/loss_values, lr_steps/lr_values; keeps the cross-epoch counters there."""
+    net.train()
+    n = len(batches)
+    phase = state.setdefault("phase", 0)
+    value = state.setdefault("value", 0.0)
+    for i, batch in enumerate(batches):
+        batch = [t.to(device) if isinstance(t, torch.Tensor) else t for t in batch]
+        last = (i == n - 1)
+        if last:
+            phase, sync = 0, True
+        else:
+            phase += 1
+            sync = (phase % accum) == 0
+        with torch.enable_grad():
+            out = net(batch)
+            loss = objective(out)
+            if sync_loss:
+                value += loss.item() / accum
+            if sync:
+                state["loss_steps"].append(state["loss_step"])
+                state["loss_values"].append(value)
+                state["loss_step"] += 1
+                value = 0.0
+            (loss / accum).backward()
+        if sync:
+            if max_norm is not None:
+                torch.nn.utils.clip_grad_norm_(net.parameters(), max_norm, foreach=False)
+            opt.step()
+            opt.zero_grad()
+            state["lr_steps"].append(state["opt_step"])
+            state["lr_values"].append(opt.param_groups[0]["lr"])
+            state["opt_step"] += 1
+            if sched is not None:
+                for _ in range(world):
+                    sched.step()
+        elif sched is not None:
+            sched._step_count += 1
+    state["phase"], state["value"] = phase, value
+
+
+@torch.no_grad()
+def eval_epoch(net, batches, *, device) -> tuple[int, int]:
+    net.eval()
+    positive = total = 0
+    for batch in batches:
+        batch = [t.to(device) if isinstance(t, torch.Tensor) else t for t in batch]
+        _, gt, logits = net(batch)
+        pr = logits.argmax(1)
+        total += pr.numel()
+        positive += int(torch.sum(gt == pr))
+    return positive, total
+
+
+def new_state() -> dict:
+    return dict(loss_steps=[], loss_values=[], lr_steps=[], lr_values=[], loss_step=0,
+                opt_step=0, accuracy_history=[])
+
+
+def run_mnist_port(*, device="cpu", seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_size=64,
+                   optimizer="adamw", max_norm=None, accum=2, epochs=2, sched_step=5, lr=1e-3,
+                   net=None, workloads=None) -> dict:
+    """The graph of tests/workloads.build_mnist_graph, as straight-line code."""
+    if workloads is None:
+        import workloads  # tests/workloads.py (on sys.path in tests and bench)
+    torch.manual_seed(seed)
+    net = net if net is not None else workloads.LeNet()
+    if optimizer == "adamw":
+        opt = torch.optim.AdamW(net.parameters(), lr=lr, foreach=False)
+    elif optimizer == "adam":
+        opt = torch.optim.Adam(net.parameters(), lr=lr, weight_decay=1e-3, foreach=False)
+    elif optimizer == "sgd":
+        opt = torch.optim.SGD(net.parameters(), lr=lr * 50, momentum=0.9, weight_decay=1e-4,
+                              nesterov=True, foreach=False)
+    else:
+        raise ValueError(optimizer)
+    sched = torch.optim.lr_scheduler.StepLR(opt, sched_step, gamma=0.5)
+    train = workloads.synthetic_classification(n_train, (1, 28, 28), 10, seed + 1)
+    val = workloads.synthetic_classification(n_val, (1, 28, 28), 10, seed + 2)
+    net.to(device)
+    objective = workloads.CrossEntropy()
+    tl = torch.utils.data.DataLoader(train, batch_size=batch_size, shuffle=False)
+    vl = torch.utils.data.DataLoader(val, batch_size=batch_size, shuffle=False)
+    state = new_state()
+    for epoch in range(epochs):
+        train_epoch(net, objective, opt, sched, tl, accum=accum, max_norm=max_norm,
+                    device=device, state=state)
+        pos, tot = eval_epoch(net, vl, device=device)
+        state["accuracy_history"].append((epoch, pos, tot))
+        # eval iterations advance accelerate's accumulation phase too (module.py:138,211);
+        # the last eval batch resets it
+        state["phase"] = 0
+    state["params"] = {k: p.detach().cpu().clone() for k, p in net.named_parameters()}
+    state["net"], state["opt"] = net, opt
+    return state
+
+
+def time_steps(net, objective, opt, batch, *, steps: int, warmup: int, max_norm, device):
+    """Seconds per step of the reference arithmetic on ``device`` for one fixed batch
+    (bench.py's cpu_baseline / --impl reference)."""
+    net.train()
+
+    def one():
+        out = net([t.to(device) for t in batch])
+        loss = objective(out)
+        loss.item()
+        loss.backward()
+        if max_norm is not None:
+            torch.nn.utils.clip_grad_norm_(net.parameters(), max_norm, foreach=False)
+        opt.step()
+        opt.zero_grad()
+
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    return (time.perf_counter() - t0) / steps

@@ -59,6 +59,10 @@ class Optimizer(Capsule):
             self._iter_idx += 1
 
     def destroy(self, attrs: Attributes | None = None) -> None:
+        # leave the user's torch optimizer with ordinary per-parameter state
+        export = getattr(self._optimizer, "_export_state", None)
+        if export is not None:
+            export()
         prepared = self._accelerator._optimizers
         for i, candidate in enumerate(prepared):
             if candidate is self._optimizer:

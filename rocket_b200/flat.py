@@ -206,6 +206,7 @@ class EngineOptimizer:
         fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)
         self._zeroed_by_step = True
         self._state_dirty = True
+        self.optimizer._opt_called = True   # what torch's LRScheduler checks before warning
 
     # ---- gradient adoption -----------------------------------------------------------------------
     def _adopt_grads(self) -> None:
