@@ -32,6 +32,69 @@ import time
 import torch
 
 
+class OracleOptimizer:
+    """The C oracle (oracle/step_oracle.c) wearing a torch.optim interface.
+
+    Parameters may live on any device; each step copies gradients to the host, runs the
+    plain-C restatement of torch's CPU arithmetic there (clip coefficient, AdamW / Adam / SGD
+    update) and writes the parameters back.  Slow by construction -- it is the checker for
+    the CUDA engine in GPU parity tests, where both arms share the same GPU forward/backward
+    and must then agree to the last bit (no clipping) or to the clip-norm's last ulp.
+    """
+
+    def __init__(self, inner: torch.optim.Optimizer, max_norm=None):
+        import numpy as np
+        import oracle
+        self._np, self._oracle = np, oracle
+        self.inner, self.max_norm = inner, max_norm
+        self.param_groups = inner.param_groups
+        self.kind = {torch.optim.AdamW: "adamw", torch.optim.Adam: "adam",
+                     torch.optim.SGD: "sgd"}[type(inner)]
+        self.state = {}
+        self.steps = 0
+
+    def step(self):
+        np, oracle = self._np, self._oracle
+        params = [p for g in self.param_groups for p in g["params"] if p.grad is not None]
+        grads = [p.grad.detach().cpu().numpy().reshape(-1).copy() for p in params]
+        total = None
+        if self.max_norm is not None:
+            total, _ = oracle.l2norm_multi(grads, 1.0)
+        self.steps += 1
+        i = 0
+        for group in self.param_groups:
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                g = grads[i]
+                i += 1
+                st = self.state.setdefault(p, {})
+                host = p.detach().cpu().numpy().reshape(-1).copy()
+                if self.kind == "sgd":
+                    first = "buf" not in st
+                    if group["momentum"] != 0 and first:
+                        st["buf"] = np.zeros_like(host)
+                    oracle.sgd_step(host, g, st.get("buf"), lr=group["lr"],
+                                    momentum=group["momentum"], dampening=group["dampening"],
+                                    weight_decay=group["weight_decay"],
+                                    nesterov=group["nesterov"], first_step=first,
+                                    total_norm=total, max_norm=self.max_norm or 0.0)
+                else:
+                    if "m" not in st:
+                        st["m"], st["v"], st["step"] = np.zeros_like(host), np.zeros_like(host), 0
+                    st["step"] += 1
+                    oracle.adam_step(host, g, st["m"], st["v"], lr=group["lr"],
+                                     beta1=group["betas"][0], beta2=group["betas"][1],
+                                     eps=group["eps"], weight_decay=group["weight_decay"],
+                                     step=st["step"], decoupled=self.kind == "adamw",
+                                     total_norm=total, max_norm=self.max_norm or 0.0)
+                with torch.no_grad():
+                    p.copy_(torch.from_numpy(host).view(p.shape))
+
+    def zero_grad(self, set_to_none=True):
+        self.inner.zero_grad(set_to_none=set_to_none)
+
+
 def train_epoch(net, objective, opt, sched, batches, *, accum: int, max_norm, device,
                 state: dict, world: int = 1, sync_loss: bool = True) -> None:
     """One pass over ``batches`` (a sized iterable of CPU batches). Appends to ``state``:
@@ -60,7 +123,7 @@ def train_epoch(net, objective, opt, sched, batches, *, accum: int, max_norm, de
                 value = 0.0
             (loss / accum).backward()
         if sync:
-            if max_norm is not None:
+            if max_norm is not None and not isinstance(opt, OracleOptimizer):
                 torch.nn.utils.clip_grad_norm_(net.parameters(), max_norm, foreach=False)
             opt.step()
             opt.zero_grad()
@@ -95,7 +158,7 @@ def new_state() -> dict:
 
 def run_mnist_port(*, device="cpu", seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_size=64,
                    optimizer="adamw", max_norm=None, accum=2, epochs=2, sched_step=5, lr=1e-3,
-                   net=None, workloads=None) -> dict:
+                   net=None, workloads=None, optimizer_impl="torch") -> dict:
     """The graph of tests/workloads.build_mnist_graph, as straight-line code."""
     if workloads is None:
         import workloads  # tests/workloads.py (on sys.path in tests and bench)
@@ -111,6 +174,9 @@ def run_mnist_port(*, device="cpu", seed=0, n_train=64 * 24, n_val=64 * 5 + 13, 
     else:
         raise ValueError(optimizer)
     sched = torch.optim.lr_scheduler.StepLR(opt, sched_step, gamma=0.5)
+    if optimizer_impl == "oracle":
+        opt._opt_called = True                      # keep LRScheduler's order check quiet
+        opt = OracleOptimizer(opt, max_norm)
     train = workloads.synthetic_classification(n_train, (1, 28, 28), 10, seed + 1)
     val = workloads.synthetic_classification(n_val, (1, 28, 28), 10, seed + 2)
     net.to(device)

@@ -42,16 +42,33 @@ CASES = {
 }
 
 
+# Two comparison arms, both sharing the engine's GPU forward/backward (cuDNN deterministic):
+#   "oracle"     optimizer arithmetic = oracle/step_oracle.c, i.e. torch's CPU kernels restated
+#                (the reference's step as pinned by the CPU suite).  The CUDA kernels spell the
+#                same rounding sequence, so parameters must agree BIT FOR BIT without clipping,
+#                and to the clip norm's last ulp with it.
+#   "torch_cuda" optimizer arithmetic = torch.optim(foreach=False) CUDA kernels.  torch's CUDA
+#                elementwise kernels round differently from its own CPU kernels (division by a
+#                scalar becomes a multiply by the reciprocal, addcdiv/addcmul group the product
+#                differently); Adam's normalisation amplifies those ulps over steps.  Measured
+#                on B200: torch-CUDA vs torch-CPU-semantics = 1.1e-5 after 26 AdamW steps, and
+#                the engine sits exactly on the CPU side of that gap.  Bar here: 1e-4.
+ARMS = {"oracle": 1e-5, "torch_cuda": 1e-4}
+
+
 @pytest.mark.parametrize("name", list(CASES))
 @pytest.mark.parametrize("clip_via", ["capsule", "kwarg"])
-def test_capsule_graph_matches_port_on_gpu(name, clip_via):
+@pytest.mark.parametrize("arm", list(ARMS))
+def test_capsule_graph_matches_port_on_gpu(name, clip_via, arm):
     import rocket_b200 as rk
     from rocket_b200.metrics import Accuracy
     from rocket_b200.tracking import MemoryTracker
     kw = CASES[name]
     if kw["max_norm"] is None and clip_via == "kwarg":
         pytest.skip("no clipping in this case")
-    port = looper_port.run_mnist_port(device="cuda", workloads=workloads, **kw)
+    port = looper_port.run_mnist_port(
+        device="cuda", workloads=workloads,
+        optimizer_impl="oracle" if arm == "oracle" else "torch", **kw)
 
     tracker = MemoryTracker("memory")
     launcher, h = workloads.build_mnist_graph(rk, tracker_backend=tracker, clip_via=clip_via,
@@ -65,15 +82,21 @@ def test_capsule_graph_matches_port_on_gpu(name, clip_via):
     # Meter counts: integers, bit-exact
     assert [tuple(x) for x in h["accuracy"].history] == \
         [tuple(x) for x in port["accuracy_history"]]
-    # parameters after N optimizer steps: <= 1e-5 relative, per tensor and overall
+    # parameters after N optimizer steps, per tensor and overall
+    tol = ARMS[arm]
     mine = dict(h["net"].named_parameters())
     num = den = 0.0
     for k, want in port["params"].items():
         got = mine[k].detach().cpu()
-        assert _rel(got, want) <= 1e-5, (k, _rel(got, want))
+        if arm == "oracle" and kw["max_norm"] is None:
+            assert torch.equal(got, want), f"{k}: not bit-exact against the oracle arm"
+        assert _rel(got, want) <= tol, (k, _rel(got, want))
         num += float((got - want).pow(2).sum())
         den += float(want.pow(2).sum())
-    assert (num / den) ** 0.5 <= 1e-5
+    assert (num / den) ** 0.5 <= tol
+    if arm == "oracle":
+        # the loss the engine accumulated on the device equals the host-side doubles
+        assert [v for _, v in losses] == port["loss_values"]
 
 
 def test_user_metric_through_gather_path_matches_device_metric():
