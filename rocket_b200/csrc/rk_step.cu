@@ -13,6 +13,7 @@
 // same gradients and clip coefficient.  See oracle/step_oracle.c for the restatement
 // this is tested against.
 #include <math.h>
+#include <stdlib.h>
 
 #include "rk_common.cuh"
 
@@ -91,9 +92,44 @@ struct SgdOp {
   }
 };
 
+// ---- global memory access: explicit ld.global / st.global (pointers come out of the
+// descriptor table, so the compiler would otherwise emit generic LD/ST) ------------------
+template <int HINT> __device__ __forceinline__ float4 ldg4(const float* p) {
+  float4 r;
+  if (HINT == 1)
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  else if (HINT == 2)
+    asm volatile("ld.global.cs.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  else
+    asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+template <int HINT> __device__ __forceinline__ void stg4(float* p, const float4& v) {
+  if (HINT == 2)
+    asm volatile("st.global.cs.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+  else
+    asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float ldg1(const float* p) {
+  float r;
+  asm volatile("ld.global.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg1(float* p, float v) {
+  asm volatile("st.global.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory");
+}
+
 // ---- the chunk walker ------------------------------------------------------------------
-template <class Op, class Table>
-__global__ void __launch_bounds__(STEP_THREADS)
+// U   : 128-bit loads per stream a thread keeps in flight (U * 4 streams LDG.128)
+// MINB: resident CTAs per SM the register allocator must allow
+// HINT: 0 default caching, 1 loads skip L1 allocation, 2 streaming (evict-first) ld/st
+template <class Op, class Table, int U, int MINB, int HINT>
+__global__ void __launch_bounds__(STEP_THREADS, MINB)
 rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table table,
                const float* __restrict__ total_norm, float max_norm, float grad_scale,
                int zero_grads) {
@@ -121,56 +157,58 @@ rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table tabl
     const int64_t base = (int64_t)(c - prefix[t]) * RK_STEP_CHUNK;
     const int64_t rem = d.numel - base;
     const int count = rem < RK_STEP_CHUNK ? (int)rem : RK_STEP_CHUNK;
-    float* __restrict__ P = d.p + base;
-    float* __restrict__ G = d.g + base;
-    float* __restrict__ M = d.m + base;
-    float* __restrict__ V = Op::kHasV ? d.v + base : nullptr;
+    float* P = d.p + base;
+    float* G = d.g + base;
+    float* M = d.m + base;
+    float* V = Op::kHasV ? d.v + base : nullptr;
     const bool has_m = d.m != nullptr;  // plain SGD keeps no state
 
     if (d.flags & RK_TENSOR_VEC4) {
       const int nvec = count >> 2;
-      float4 p4[STEP_UNROLL], g4[STEP_UNROLL], m4[STEP_UNROLL], v4[STEP_UNROLL];
+      for (int i0 = tid; i0 < nvec; i0 += STEP_THREADS * U) {
+        float4 p4[U], g4[U], m4[U], v4[U];
 #pragma unroll
-      for (int k = 0; k < STEP_UNROLL; ++k) {
-        const int i = tid + k * STEP_THREADS;
-        if (i < nvec) {
-          p4[k] = reinterpret_cast<const float4*>(P)[i];
-          g4[k] = reinterpret_cast<const float4*>(G)[i];
-          if (has_m) m4[k] = reinterpret_cast<const float4*>(M)[i];
-          if (Op::kHasV) v4[k] = reinterpret_cast<const float4*>(V)[i];
+        for (int k = 0; k < U; ++k) {
+          const int i = i0 + k * STEP_THREADS;
+          if (i < nvec) {
+            p4[k] = ldg4<HINT>(P + 4 * i);
+            g4[k] = ldg4<HINT>(G + 4 * i);
+            if (has_m) m4[k] = ldg4<HINT>(M + 4 * i);
+            if (Op::kHasV) v4[k] = ldg4<HINT>(V + 4 * i);
+          }
         }
-      }
 #pragma unroll
-      for (int k = 0; k < STEP_UNROLL; ++k) {
-        const int i = tid + k * STEP_THREADS;
-        if (i < nvec) {
-          op(p4[k].x, prolog_g(g4[k].x, pr), m4[k].x, v4[k].x);
-          op(p4[k].y, prolog_g(g4[k].y, pr), m4[k].y, v4[k].y);
-          op(p4[k].z, prolog_g(g4[k].z, pr), m4[k].z, v4[k].z);
-          op(p4[k].w, prolog_g(g4[k].w, pr), m4[k].w, v4[k].w);
-          reinterpret_cast<float4*>(P)[i] = p4[k];
-          if (has_m) reinterpret_cast<float4*>(M)[i] = m4[k];
-          if (Op::kHasV) reinterpret_cast<float4*>(V)[i] = v4[k];
-          if (zero_grads) reinterpret_cast<float4*>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < U; ++k) {
+          const int i = i0 + k * STEP_THREADS;
+          if (i < nvec) {
+            op(p4[k].x, prolog_g(g4[k].x, pr), m4[k].x, v4[k].x);
+            op(p4[k].y, prolog_g(g4[k].y, pr), m4[k].y, v4[k].y);
+            op(p4[k].z, prolog_g(g4[k].z, pr), m4[k].z, v4[k].z);
+            op(p4[k].w, prolog_g(g4[k].w, pr), m4[k].w, v4[k].w);
+            stg4<HINT>(P + 4 * i, p4[k]);
+            if (has_m) stg4<HINT>(M + 4 * i, m4[k]);
+            if (Op::kHasV) stg4<HINT>(V + 4 * i, v4[k]);
+            if (zero_grads) stg4<HINT>(G + 4 * i, make_float4(0.f, 0.f, 0.f, 0.f));
+          }
         }
       }
       const int i = (nvec << 2) + tid;  // < 4 leftover elements
       if (i < count) {
-        float p = P[i], m = has_m ? M[i] : 0.f, v = Op::kHasV ? V[i] : 0.f;
-        op(p, prolog_g(G[i], pr), m, v);
-        P[i] = p;
-        if (has_m) M[i] = m;
-        if (Op::kHasV) V[i] = v;
-        if (zero_grads) G[i] = 0.f;
+        float p = ldg1(P + i), m = has_m ? ldg1(M + i) : 0.f, v = Op::kHasV ? ldg1(V + i) : 0.f;
+        op(p, prolog_g(ldg1(G + i), pr), m, v);
+        stg1(P + i, p);
+        if (has_m) stg1(M + i, m);
+        if (Op::kHasV) stg1(V + i, v);
+        if (zero_grads) stg1(G + i, 0.f);
       }
     } else {
       for (int i = tid; i < count; i += STEP_THREADS) {
-        float p = P[i], m = has_m ? M[i] : 0.f, v = Op::kHasV ? V[i] : 0.f;
-        op(p, prolog_g(G[i], pr), m, v);
-        P[i] = p;
-        if (has_m) M[i] = m;
-        if (Op::kHasV) V[i] = v;
-        if (zero_grads) G[i] = 0.f;
+        float p = ldg1(P + i), m = has_m ? ldg1(M + i) : 0.f, v = Op::kHasV ? ldg1(V + i) : 0.f;
+        op(p, prolog_g(ldg1(G + i), pr), m, v);
+        stg1(P + i, p);
+        if (has_m) stg1(M + i, m);
+        if (Op::kHasV) stg1(V + i, v);
+        if (zero_grads) stg1(G + i, 0.f);
       }
     }
   }
@@ -179,6 +217,34 @@ rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table tabl
 // ---- host side ---------------------------------------------------------------------------
 static inline bool need_m(const AdamDev&) { return true; }
 static inline bool need_m(const SgdDev& g) { return (g.flags & SGD_HAS_MOM) != 0; }
+
+template <class Op, class Table, int U, int MINB, int HINT>
+static int launch_variant(const rk_plan_header* h, const void* plan_dev, const Table& table,
+                          const float* total_norm_dev, float max_norm, float grad_scale,
+                          int zero_grads, void* stream) {
+  auto kernel = rk_step_kernel<Op, Table, U, MINB, HINT>;
+  int grid = 0;
+  int rc = rk_persistent_grid((const void*)kernel, STEP_THREADS, 0, h->n_chunks_step, &grid);
+  if (rc) return rc;
+  kernel<<<grid, STEP_THREADS, 0, (cudaStream_t)stream>>>(
+      (const char*)plan_dev, table, total_norm_dev, max_norm, grad_scale, zero_grads);
+  return 0;
+}
+
+// Tuning variants (selected with RK_STEP_VARIANT while measuring; the default is the one
+// the ncu captures under profiles/ justify).
+#ifndef RK_STEP_DEFAULT_VARIANT
+#define RK_STEP_DEFAULT_VARIANT 4
+#endif
+static int step_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("RK_STEP_VARIANT");
+    v = e ? atoi(e) : RK_STEP_DEFAULT_VARIANT;
+  }
+  return v;
+}
+
 template <class Op, class Table>
 static int launch_step(const void* plan_host, const void* plan_dev, const Table& table,
                        const float* total_norm_dev, float max_norm, float grad_scale,
@@ -199,12 +265,30 @@ static int launch_step(const void* plan_host, const void* plan_dev, const Table&
                  "%s: tensor %d has no v (exp_avg_sq) buffer", who, i);
     }
   }
-  int grid = 0;
-  int rc = rk_persistent_grid((const void*)rk_step_kernel<Op, Table>, STEP_THREADS, 0,
-                              h->n_chunks_step, &grid);
+  int rc;
+#define RK_V(U, MINB, HINT)                                                              \
+  rc = launch_variant<Op, Table, U, MINB, HINT>(h, plan_dev, table, total_norm_dev,      \
+                                                max_norm, grad_scale, zero_grads, stream)
+  switch (step_variant()) {
+    default:
+    case 0: RK_V(4, 2, 0); break;
+    case 1: RK_V(2, 4, 0); break;
+    case 2: RK_V(1, 6, 0); break;
+    case 3: RK_V(1, 8, 0); break;
+    case 4: RK_V(2, 3, 0); break;
+    case 5: RK_V(2, 4, 1); break;
+    case 6: RK_V(2, 4, 2); break;
+    case 7: RK_V(1, 6, 2); break;
+    case 8: RK_V(4, 2, 2); break;
+    case 9: RK_V(1, 5, 1); break;
+    case 10: RK_V(2, 2, 0); break;
+    case 11: RK_V(3, 2, 0); break;
+    case 12: RK_V(2, 3, 2); break;
+    case 13: RK_V(2, 3, 1); break;
+    case 14: RK_V(3, 3, 0); break;
+  }
+#undef RK_V
   if (rc) return rc;
-  rk_step_kernel<Op, Table><<<grid, STEP_THREADS, 0, (cudaStream_t)stream>>>(
-      (const char*)plan_dev, table, total_norm_dev, max_norm, grad_scale, zero_grads);
   RK_CUDA(cudaGetLastError());
   g_rk_launches.fetch_add(1);
   return 0;

@@ -27,7 +27,7 @@ class DeferredScalar:
 
     def _resolve(self):
         if self._value is None:
-            if self._event is not None:
+            if self._event is not None and not self._event.query():
                 self._event.synchronize()
             raw = self._slot.item() if self._slot.numel() == 1 else self._slot.tolist()
             self._value = self._finalize(raw) if self._finalize is not None else raw

@@ -145,18 +145,32 @@ def test_stager_roundtrip_and_ring_reuse():
 
 
 def test_deferred_loss_does_not_sync_per_step():
-    """Count host synchronisations in steady state with torch.profiler: the engine-owned
-    part of a step must not call cudaStreamSynchronize / cudaDeviceSynchronize."""
+    """Host synchronisations must not grow with the number of steps.  Counted with
+    torch.profiler (nsys is not on the image): cudaStreamSynchronize / cudaDeviceSynchronize /
+    cudaEventSynchronize calls of a 10-step run and of a 40-step run of the same graph must be
+    equal -- what remains is set-up (moving the model, uploading the plan) and the one
+    counter read per epoch."""
     import rocket_b200 as rk
+    from rocket_b200.metrics import Accuracy
     from torch.profiler import ProfilerActivity, profile
-    kw = dict(optimizer="adamw", max_norm=1.0, accum=1, epochs=1, n_train=64 * 30,
-              clip_via="kwarg")
-    launcher, h = workloads.build_mnist_graph(rk, **kw)
-    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
-        launcher.launch()
-    names = [e.key for e in prof.key_averages()]
-    counts = {e.key: e.count for e in prof.key_averages()}
-    syncs = sum(c for k, c in counts.items()
-                if "StreamSynchronize" in k or "DeviceSynchronize" in k)
-    # setup/teardown and the epoch-end counter read may sync; 30 train + 6 eval steps may not
-    assert syncs <= 12, (syncs, [n for n in names if "ynchronize" in n])
+
+    def syncs(n_steps: int):
+        kw = dict(optimizer="adamw", max_norm=1.0, accum=1, epochs=1, n_train=64 * n_steps,
+                  clip_via="kwarg")
+        launcher, _ = workloads.build_mnist_graph(rk, accuracy_cls=Accuracy, **kw)
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            launcher.launch()
+        # The stager's worker thread legitimately waits (off the critical path) for the
+        # previous H2D out of a pinned slot; only threads that launch kernels -- the Python
+        # thread and autograd's -- are the step's critical path.
+        events = list(prof.events())
+        compute_threads = {e.thread for e in events if e.name == "cudaLaunchKernel"}
+        out: dict = {}
+        for e in events:
+            if "Synchronize" in e.name and e.thread in compute_threads:
+                out[e.name] = out.get(e.name, 0) + 1
+        return out
+
+    syncs(5)                                  # warm the caches (cudnn, allocator)
+    short, long = syncs(10), syncs(40)
+    assert sum(short.values()) == sum(long.values()), (short, long)
