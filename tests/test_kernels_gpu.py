@@ -144,6 +144,40 @@ def test_adam_step_bit_exact(case, clip, name):
                     f"tensor {i} ({sizes[i]} elems) stream {'pgmv'[k]} step {step}"
 
 
+def test_adam_step_zeros_denormals_and_specials_bit_exact():
+    """Exact zeros (dead units), denormals, huge values, infinities and NaNs in every stream:
+    the division / sqrt wrappers must give the same bits as the IEEE oracle."""
+    be = _backend()
+    from rocket_b200.backend import TensorSpec
+    n = 8192 + 5
+    g = torch.Generator().manual_seed(77)
+    hp_, hg, hm, hv = (torch.randn(n, generator=g) * s for s in (0.02, 1e-2, 1e-3, 1e-3))
+    hv = hv * hv
+    specials = torch.tensor([0.0, -0.0, 1e-45, -1e-45, 1e-39, 3e-38, 1e38, -1e38, 1e-30,
+                             float("inf"), float("-inf"), float("nan"), 1.0, -1.0])
+    k = specials.numel()
+    for j, t in enumerate((hp_, hg, hm, hv)):
+        for r in range(4):                       # every special against several partners
+            idx = torch.arange(k) * 7 + 100 * (r + 1) + 13 * j
+            t[idx] = specials.roll(r * (j + 1)) if t is not hv else specials.roll(r).abs()
+    hg[::5] = 0.0                                 # 20 % dead gradients
+    hm[::5] = 0.0
+    hv[::5] = 0.0
+    for hp in (ADAM_CASES[0], dict(ADAM_CASES[2], eps=0.0)):
+        host = [t.numpy().copy() for t in (hp_, hg, hm, hv)]
+        spec = TensorSpec(*[torch.from_numpy(a.copy()).to(DEV) for a in host], group=0)
+        plan = be.make_plan([spec])
+        be.adam_step(plan, [dict(hp, step=3)], None, 0.0, 1.0, False)
+        torch.cuda.synchronize()
+        oracle.adam_step(*host, lr=hp["lr"], beta1=hp["beta1"], beta2=hp["beta2"],
+                         eps=hp["eps"], weight_decay=hp["weight_decay"], step=3,
+                         decoupled=hp["decoupled"])
+        for name, t, a in zip("pgmv", (spec.p, spec.g, spec.m, spec.v), host):
+            got = t.cpu().numpy()
+            same = (_bits(got) == _bits(a)) | (np.isnan(got) & np.isnan(a))
+            assert same.all(), (name, np.nonzero(~same)[0][:5], got[~same][:5], a[~same][:5])
+
+
 SGD_CASES = [
     dict(lr=0.1, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False),
     dict(lr=0.1, momentum=0.9, dampening=0.0, weight_decay=1e-4, nesterov=False),
