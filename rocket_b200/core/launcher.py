@@ -57,7 +57,7 @@ class Launcher(Dispatcher):
         self._load_capsules = True
 
     # ---- project directory --------------------------------------------------------------
-    def _resolve_project_dir(self, engine) -> None:
+    def _resolve_project_dir(self) -> None:
         """``logs/<tag>`` or, with versioning, ``logs/<tag>/v<last+1>``; rank 0 decides and
         broadcasts (reference launcher.py:125-150)."""
         if self._tag is None:
@@ -77,7 +77,8 @@ class Launcher(Dispatcher):
                 if versions:
                     last = versions[-1]
             self._project_dir = os.path.join(root, f"v{last + 1}")
-        self._project_dir = engine.broadcast_object_list([self._project_dir], from_process=0)[0]
+        self._project_dir = self._accelerator.broadcast_object_list(
+            [self._project_dir], from_process=0)[0]
 
     def _create_project_dir(self) -> None:
         if self._tag is None:
@@ -93,9 +94,9 @@ class Launcher(Dispatcher):
             mixed_precision=self._mixed_precision,
             gradient_accumulation_steps=self._gradient_accumulation_steps,
             project_dir=None)
-        self._resolve_project_dir(engine)
-        engine.project_dir = self._project_dir
         self.accelerate(engine)
+        self._resolve_project_dir()
+        engine.project_dir = self._project_dir
         self._create_project_dir()
         self._num_procs = attrs.launcher.num_procs
         self._num_nodes = attrs.launcher.num_nodes

@@ -58,7 +58,7 @@ class Tracker(Capsule):
         Capsule.reset(self, attrs=attrs)
         if attrs is None or attrs.tracker is None:
             return
-        self.log(attrs.tracker.images, attrs.tracker.scalars, block=True)
+        self._log(attrs.tracker.images, attrs.tracker.scalars, block=True)
         del attrs.tracker
 
     def destroy(self, attrs: Attributes = None) -> None:
@@ -77,8 +77,12 @@ class Tracker(Capsule):
             self._logger.debug(f"Successfully logged scalars to {self._backend}")
             self._pending.pop(0)
 
-    def log(self, images: List[Attributes] | None, scalars: List[Attributes] | None,
-            block: bool = False) -> None:
+    def log(self, images: List[Attributes] | None, scalars: List[Attributes] | None) -> None:
+        """Forward records to the backend (reference tracker.py:201-254); scalar records whose
+        values are still in flight are kept for the next call."""
+        self._log(images, scalars, block=False)
+
+    def _log(self, images, scalars, block: bool) -> None:
         main = self._accelerator.is_main_process
         if images and main:
             try:
