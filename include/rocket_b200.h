@@ -116,6 +116,36 @@ int rk_l2norm_multi(const void* plan_host, const void* plan_dev, float grad_scal
                     void* scratch_dev, float* total_norm_dev,
                     float* tensor_norms_dev, void* stream);
 
+/* ---- K1 again, for callers that cannot supply scratch memory -------------------------------
+ * No counterpart in the reference: this entry point exists only because of who may call
+ * this library.  Some hosts cannot allocate device memory at the point where they need the
+ * norm: a runtime that handed the whole GPU to its own memory pool at start-up and forbids
+ * driver allocations afterwards, or a thin foreign-language binding (cgo, JNI, a plugin
+ * ABI) that only ever holds the device pointers its framework passes in -- the gradients
+ * and a place for the result -- and has no way to create or own a buffer of its own.
+ *
+ * Same kernel and same result as rk_l2norm_multi, but the scratch (per-chunk partials,
+ * per-tensor norms, completion ticket) is a fixed array inside the library's device image:
+ * RK_STATIC_SCRATCH_BYTES on every GPU that loads the library, held until the process
+ * exits.  The call allocates nothing on the device, now or later (no cudaMalloc, no
+ * cudaFree, no allocating library routine); the caller still passes the plan, the
+ * gradients it describes and the output pointers.
+ *   - Tensor lists whose plan needs more scratch than that (rk_plan_query's
+ *     scratch_bytes; roughly 8 bytes per norm chunk + 4 per tensor, i.e. beyond ~100K
+ *     tensors) are refused with RK_ERR_TOO_LARGE and a message; nothing is launched.
+ *   - The first call on each device looks up the array's device address (that device must
+ *     be current, as for every call here).  Make that first call before starting any
+ *     stream capture.
+ *   - All calls on a device share the one array.  It keeps the previous call's contents;
+ *     the entry point clears the part that must start at zero itself.  Two calls whose
+ *     kernels can overlap on the GPU (different streams, or different host threads without
+ *     ordering between them) race on it: serialise them on one stream or with events.
+ *   - total_norm_dev must not be NULL (there is no caller-visible scratch to read the
+ *     result from).                                                                        */
+#define RK_STATIC_SCRATCH_BYTES (1u << 20)
+int rk_l2norm_multi_static(const void* plan_host, const void* plan_dev, float grad_scale,
+                           float* total_norm_dev, float* tensor_norms_dev, void* stream);
+
 /* ---- K2: fused multi-tensor Adam / AdamW step ---------------------------------
  * One pass over HBM doing, per element and in this order:
  *   g  = g * grad_scale                      (1/world_size; skipped when 1.0)

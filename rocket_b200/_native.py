@@ -18,7 +18,8 @@ RK_MAX_GROUPS = 64
 RK_TENSOR_SKIP = 1
 EXPORTS = [
     "rk_version", "rk_last_error", "rk_launch_count", "rk_plan_query", "rk_plan_build",
-    "rk_l2norm_multi", "rk_adamw_step_multi", "rk_adam_derive", "rk_sgd_step_multi",
+    "rk_l2norm_multi", "rk_l2norm_multi_static", "rk_adamw_step_multi", "rk_adam_derive",
+    "rk_sgd_step_multi",
     "rk_meter_argmax_count", "rk_scalar_accumulate", "rk_stage_create", "rk_stage_submit",
     "rk_stage_wait", "rk_stage_release", "rk_stage_destroy",
 ]
@@ -65,6 +66,8 @@ def load() -> ctypes.CDLL:
     lib.rk_plan_build.argtypes = [POINTER(TensorDesc), c_int, c_void_p, c_size_t]
     lib.rk_l2norm_multi.argtypes = [c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
                                     c_void_p]
+    lib.rk_l2norm_multi_static.argtypes = [c_void_p, c_void_p, c_float, c_void_p, c_void_p,
+                                           c_void_p]
     lib.rk_adamw_step_multi.argtypes = [c_void_p, c_void_p, POINTER(AdamGroup), c_int, c_void_p,
                                         c_float, c_float, c_int, c_void_p]
     lib.rk_adam_derive.argtypes = [POINTER(AdamGroup), POINTER(c_float), POINTER(c_int)]

@@ -6,6 +6,8 @@
 //          partials -> per-tensor norms -> total norm.  No float atomics anywhere, so
 //          the result does not depend on CTA scheduling and is bit-identical on every
 //          rank that holds the same gradients.
+#include <mutex>
+
 #include "rk_common.cuh"
 
 #define NORM_THREADS 256
@@ -164,6 +166,75 @@ extern "C" int rk_l2norm_multi(const void* plan_host, const void* plan_dev, floa
   if (rc) return rc;
   rk_l2norm_kernel<<<grid, NORM_THREADS, 0, (cudaStream_t)stream>>>(
       (const char*)plan_dev, grad_scale, (char*)scratch_dev, total_norm_dev, tensor_norms_dev);
+  RK_CUDA(cudaGetLastError());
+  g_rk_launches.fetch_add(1);
+  return 0;
+}
+
+// ---- the same norm for callers that have no scratch buffer to give ---------------------
+// Scratch for rk_l2norm_multi_static lives in this module's own device image: one array per
+// GPU that loads the library, held until the process exits.  In host code `g_static_scratch`
+// is only a stand-in for the symbol, not a device address; the address is looked up once per
+// device with cudaGetSymbolAddress (with that device current) and handed to the kernel.
+static __device__ __align__(256) unsigned char g_static_scratch[RK_STATIC_SCRATCH_BYTES];
+
+#define RK_MAX_DEVICES 64
+static std::mutex g_static_mu;
+static void* g_static_ptr[RK_MAX_DEVICES];   // device address of g_static_scratch, per device
+static int g_static_resident[RK_MAX_DEVICES];  // persistent grid size, per device
+
+static int static_setup_current_device(void** scratch, int* resident) {
+  int dev = -1;
+  RK_CUDA(cudaGetDevice(&dev));
+  RK_REQUIRE(dev >= 0 && dev < RK_MAX_DEVICES, RK_ERR_UNSUPPORTED,
+             "rk_l2norm_multi_static: device ordinal %d not supported (max %d)", dev,
+             RK_MAX_DEVICES - 1);
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    RK_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    RK_REQUIRE(p != nullptr, RK_ERR_STATE, "cudaGetSymbolAddress returned a null address");
+    int sms = 0, per_sm = 0;
+    RK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    RK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_l2norm_kernel,
+                                                          NORM_THREADS, 0));
+    RK_REQUIRE(sms > 0 && per_sm > 0, RK_ERR_STATE, "norm kernel does not fit on an SM");
+    g_static_resident[dev] = sms * per_sm;
+    g_static_ptr[dev] = p;
+  }
+  *scratch = g_static_ptr[dev];
+  *resident = g_static_resident[dev];
+  return 0;
+}
+
+extern "C" int rk_l2norm_multi_static(const void* plan_host, const void* plan_dev,
+                                      float grad_scale, float* total_norm_dev,
+                                      float* tensor_norms_dev, void* stream) {
+  RK_REQUIRE(plan_host && plan_dev, RK_ERR_INVALID, "rk_l2norm_multi_static: null plan");
+  RK_REQUIRE(total_norm_dev, RK_ERR_INVALID,
+             "rk_l2norm_multi_static: total_norm_dev is null (the result has nowhere to go)");
+  const rk_plan_header* h = (const rk_plan_header*)plan_host;
+  RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID,
+             "rk_l2norm_multi_static: bad plan magic");
+  RK_REQUIRE(h->scratch_bytes <= RK_STATIC_SCRATCH_BYTES, RK_ERR_TOO_LARGE,
+             "rk_l2norm_multi_static: this tensor list needs %u bytes of scratch (%d norm "
+             "chunks, %d tensors) but the built-in scratch holds %u; use rk_l2norm_multi "
+             "with a caller-provided buffer",
+             h->scratch_bytes, h->n_chunks_norm, h->n_tensors, (unsigned)RK_STATIC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  int resident = 0;
+  int rc = static_setup_current_device(&scratch, &resident);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // The array still holds whatever the previous call (possibly with another plan, hence
+  // another layout) left there.  Only the ticket has to start at zero; partials and norms
+  // are fully overwritten before they are read.
+  RK_CUDA(cudaMemsetAsync((char*)scratch + h->off_ticket, 0, 128, s));
+  int grid = h->n_chunks_norm < resident ? (h->n_chunks_norm > 0 ? h->n_chunks_norm : 1)
+                                         : resident;
+  rk_l2norm_kernel<<<grid, NORM_THREADS, 0, s>>>((const char*)plan_dev, grad_scale,
+                                                 (char*)scratch, total_norm_dev,
+                                                 tensor_norms_dev);
   RK_CUDA(cudaGetLastError());
   g_rk_launches.fetch_add(1);
   return 0;
