@@ -78,14 +78,55 @@ class GradientState:
         self.active_dataloader = self.dataloader_references[-1]
 
 
-class DataLoaderShard:
-    """accelerate.data_loader.DataLoaderShard + BatchSamplerShard, restated.
+class BatchSamplerShard(torch.utils.data.Sampler):
+    """accelerate.data_loader.BatchSamplerShard (split_batches=False, even_batches=True),
+    restated: rank r takes batches r, r+W, ...; an incomplete last round is completed, at the
+    index level, by cycling through the samples of the first round."""
 
-    Rank r receives batches r, r+W, r+2W ... of the base loader's order; with
-    `even_batches` the last round is completed by wrapping to the first batches.  One
-    batch is read ahead so `end_of_dataloader` is True while the last batch is out.
-    No device placement (the reference passes device_placement=[False]).
-    """
+    def __init__(self, batch_sampler, world, rank):
+        self.batch_sampler, self.world, self.rank = batch_sampler, world, rank
+        self.batch_size = batch_sampler.batch_size
+        self.drop_last = batch_sampler.drop_last
+
+    def __len__(self):
+        n = len(self.batch_sampler)
+        return n // self.world if self.drop_last else -(-n // self.world)
+
+    def __iter__(self):
+        W, rank, bs = self.world, self.rank, self.batch_size
+        initial, mine, idx, batch = [], [], -1, []
+        for idx, batch in enumerate(self.batch_sampler):
+            batch = list(batch)
+            if not self.drop_last and idx < W:
+                initial += batch
+            if idx % W == rank:
+                mine = batch
+            if idx % W == W - 1 and len(batch) == bs:
+                yield mine
+                mine = []
+        if self.drop_last or not initial:
+            return
+        if len(mine) == bs:
+            yield mine
+        while len(initial) < W * bs:
+            initial += initial
+        if len(batch) == bs:
+            batch = []
+            idx += 1
+        cycle = 0
+        while idx % W != 0 or len(batch) > 0:
+            end = cycle + bs - len(batch)
+            batch = batch + initial[cycle:end]
+            if idx % W == rank:
+                yield batch
+            cycle, batch = end, []
+            idx += 1
+
+
+class DataLoaderShard:
+    """accelerate.data_loader.DataLoaderShard, restated: iterates the (rank-sharded) loader
+    one batch ahead so `end_of_dataloader` is True while the last batch is out.  No device
+    placement (the reference passes device_placement=[False])."""
 
     def __init__(self, base, gradient_state, skip_batches: int = 0):
         self.base = base
@@ -95,42 +136,16 @@ class DataLoaderShard:
         self.remainder = -1
         self.dataset = base.dataset
         self.batch_size = base.batch_size
-
-    def _num_base_batches(self):
-        return len(self.base)
+        rank, world = _world()
+        if world > 1:
+            self.loader = torch.utils.data.DataLoader(
+                base.dataset, batch_sampler=BatchSamplerShard(base.batch_sampler, world, rank),
+                collate_fn=base.collate_fn, num_workers=base.num_workers)
+        else:
+            self.loader = base
 
     def __len__(self):
-        rank, world = _world()
-        n = self._num_base_batches()
-        per_rank = -(-n // world)
-        return per_rank - self.skip_batches
-
-    def _rank_batches(self):
-        rank, world = _world()
-        if world == 1:
-            yield from self.base
-            return
-        first = []
-        idx = 0
-        pending = None
-        for batch in self.base:
-            if len(first) < world:
-                first.append(batch)
-            if idx % world == rank:
-                pending = batch
-                yield batch
-                pending = None
-            idx += 1
-        # even_batches: pad the last incomplete round with the first batches
-        if idx % world != 0:
-            fill = idx % world
-            k = 0
-            while fill < world:
-                if fill == rank:
-                    yield first[k % len(first)]
-                fill += 1
-                k += 1
-        del pending
+        return len(self.loader) - self.skip_batches
 
     def __iter__(self):
         self.end_of_dataloader = False
@@ -139,7 +154,7 @@ class DataLoaderShard:
         total = len(self.base.dataset) if hasattr(self.base.dataset, "__len__") else None
         if total is not None and self.base.batch_size:
             self.remainder = total % (self.base.batch_size * world)
-        it = self._rank_batches()
+        it = iter(self.loader)
         try:
             current = next(it)
         except StopIteration:

@@ -272,46 +272,92 @@ class EngineDataLoader:
             eng._end_dataloader(self)
 
     def _iterate(self):
+        """Pipeline, for batch k:
+             reader thread : next(loader) for k+1, k+2      (collation releases the GIL)
+             stager worker : pack k+1 into a pinned slot, H2D on the copy stream
+             this thread   : hand k to the capsules, which launch the step
+        The consumer only ever waits for a copy to have been *issued*.  Reading one batch
+        ahead is also what tells `end_of_dataloader` apart (forced gradient sync on the
+        last batch), so it costs nothing extra."""
         stager = self.engine.stager
-        it = iter(self._loader)
+        reader = _Reader(self._loader, self.skip_batches, depth=2)
         try:
-            n_batches = len(self._loader)
-        except TypeError:
-            n_batches = None
-        for _ in range(self.skip_batches):
-            if next(it, None) is None:
-                return
-        index = self.skip_batches
+            def stage(data):
+                if data is None:
+                    return None
+                return stager.submit(data) if stager is not None else data
 
-        def fetch():
-            data = next(it, None)
-            if data is None:
-                return None
-            return stager.submit(data) if stager is not None else data
-
-        pending = fetch()
-        held_slot = None
-        while pending is not None:
-            index += 1
-            if n_batches is not None:
-                nxt, have_next = None, index < n_batches
-            else:                                   # unsized loader: read ahead to see the end
-                nxt = fetch()
-                have_next = nxt is not None
-            if not have_next:
-                self.end_of_dataloader = True
-            if stager is not None:
-                batch, slot = stager.collect(pending)
-            else:
-                batch, slot = pending, None
-            yield batch
-            # the consumer has enqueued all work on this batch: its slot may be recycled
-            # once the compute stream gets here
-            if stager is not None:
-                stager.release(slot)
-            if n_batches is not None:
-                pending = fetch() if have_next else None
-            else:
+            pending = stage(reader.get())
+            while pending is not None:
+                nxt = stage(reader.get())          # k+1 starts packing / copying now
+                if nxt is None:
+                    self.end_of_dataloader = True
+                if stager is not None:
+                    batch, slot = stager.collect(pending)
+                else:
+                    batch, slot = pending, None
+                yield batch
+                # the consumer has enqueued all its work on this batch: the slot may be
+                # recycled once the compute stream gets here
+                if stager is not None:
+                    stager.release(slot)
                 pending = nxt
-            held_slot = slot
-        del held_slot
+        finally:
+            reader.close()
+
+
+class _Reader:
+    """Background thread that pulls batches out of a DataLoader a few steps ahead."""
+
+    _END = object()
+
+    def __init__(self, loader, skip: int, depth: int):
+        import queue
+        import threading
+        self._q = queue.Queue(maxsize=depth)
+        self._stop = threading.Event()
+        self._queue_mod = queue
+        self._thread = threading.Thread(target=self._run, args=(loader, skip), daemon=True,
+                                        name="rocket_b200-reader")
+        self._thread.start()
+
+    def _put(self, item) -> bool:
+        while not self._stop.is_set():
+            try:
+                self._q.put(item, timeout=0.05)
+                return True
+            except self._queue_mod.Full:
+                continue
+        return False
+
+    def _run(self, loader, skip: int) -> None:
+        try:
+            it = iter(loader)
+            for _ in range(skip):
+                if next(it, self._END) is self._END:
+                    break
+            else:
+                for data in it:
+                    if not self._put(data):
+                        return
+            self._put(self._END)
+        except BaseException as exc:            # surfaces in the consumer thread
+            self._put(exc)
+
+    def get(self):
+        item = self._q.get()
+        if item is self._END:
+            self._q.put(self._END)              # stay at the end for repeated calls
+            return None
+        if isinstance(item, BaseException):
+            raise item
+        return item
+
+    def close(self) -> None:
+        self._stop.set()
+        try:
+            while True:
+                self._q.get_nowait()
+        except self._queue_mod.Empty:
+            pass
+        self._thread.join(timeout=5)
