@@ -218,3 +218,35 @@ def time_steps(net, objective, opt, batch, *, steps: int, warmup: int, max_norm,
     for _ in range(steps):
         one()
     return (time.perf_counter() - t0) / steps
+
+
+def run_generic_port(net, objective, opt, batches, *, accum: int, max_norm, device,
+                     optimizer_impl: str = "torch", autocast_dtype=None) -> dict:
+    """One train epoch of an arbitrary (net, objective, optimizer) over ``batches`` with the
+    reference's step order; optimizer arithmetic = torch's own or the C oracle."""
+    if optimizer_impl == "oracle":
+        opt._opt_called = True
+        opt = OracleOptimizer(opt, max_norm)
+    net.to(device)
+    if autocast_dtype is not None:
+        inner = net.forward
+
+        def forward(*a, **k):
+            with torch.autocast(device_type=torch.device(device).type, dtype=autocast_dtype):
+                out = inner(*a, **k)
+            return [t.float() if isinstance(t, torch.Tensor) and t.dtype == autocast_dtype else t
+                    for t in out]
+        net.forward = forward
+    state = new_state()
+    ctx = torch.autocast(device_type=torch.device(device).type, dtype=autocast_dtype) \
+        if autocast_dtype is not None else None
+    if ctx is not None:
+        ctx.__enter__()
+    try:
+        train_epoch(net, objective, opt, batches, sched=None, accum=accum, max_norm=max_norm,
+                    device=device, state=state)
+    finally:
+        if ctx is not None:
+            ctx.__exit__(None, None, None)
+    state["params"] = {k: p.detach().cpu().clone() for k, p in net.named_parameters()}
+    return state

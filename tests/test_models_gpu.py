@@ -1,0 +1,156 @@
+"""BASELINE.json configs 2-4 through the unchanged capsule API on the CUDA engine, against
+the looper port sharing the same GPU forward/backward.
+
+  config 2  ResNet-18 (num_classes=10), CIFAR-shaped, AdamW + clip, fp32
+  config 3  ResNet-50, ImageNet-shaped, bf16 autocast, SGD momentum      (small batch here)
+  config 4  GPT-2 (GPT2LMHeadModel, tied embeddings), accumulation 4, AdamW(0.9, 0.95, wd 0.1)
+            + clip 1.0, bf16 autocast                                    (small config here)
+
+Arms: "oracle" = optimizer arithmetic by oracle/step_oracle.c (bar 1e-5, bit-exact expected
+when nothing separates the arms but the norm's last ulp); "torch_cuda" = torch.optim
+foreach=False on the GPU (bar 1e-4, see tests/test_engine_gpu.py for why).
+"""
+from __future__ import annotations
+
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+import workloads
+from oracle import looper_port
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _deterministic():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.deterministic = True
+    torch.backends.cudnn.benchmark = False
+    yield
+
+
+class GPTBatch(nn.Module):
+    def __init__(self, lm):
+        super().__init__()
+        self.lm = lm
+
+    def forward(self, batch):
+        ids = batch[0]
+        return ids, self.lm(input_ids=ids).logits
+
+
+class NextToken(nn.Module):
+    def forward(self, batch):
+        ids, logits = batch
+        return F.cross_entropy(logits[:, :-1].reshape(-1, logits.shape[-1]).float(),
+                               ids[:, 1:].reshape(-1))
+
+
+def _engine_run(net, objective, opt, batches, *, accum, max_norm, mixed_precision=None):
+    import rocket_b200 as rk
+    ds = _ListDataset(batches)
+    looper = rk.Looper([
+        rk.Dataset(ds, batch_size=None, shuffle=False),
+        rk.Module(net, capsules=[rk.Loss(objective=objective),
+                                 rk.Optimizer(opt, max_grad_norm=max_norm)]),
+    ], tag="train")
+    rk.Launcher([looper], num_epochs=1, gradient_accumulation_steps=accum,
+                mixed_precision=mixed_precision,
+                destroy_process_group_after_launch=False).launch()
+    return {k: p.detach().cpu() for k, p in net.named_parameters()}
+
+
+class _ListDataset(torch.utils.data.Dataset):
+    """Pre-batched samples: DataLoader(batch_size=None) hands them through unchanged."""
+
+    def __init__(self, batches):
+        self.batches = batches
+
+    def __len__(self):
+        return len(self.batches)
+
+    def __getitem__(self, i):
+        return self.batches[i]
+
+
+def _compare(mine, want, tol, exact=False):
+    num = den = 0.0
+    for k, w in want.items():
+        g = mine[k]
+        if exact:
+            assert torch.equal(g, w), k
+        rel = float((g - w).norm() / (w.norm() + 1e-30))
+        assert rel <= tol, (k, rel)
+        num += float((g - w).pow(2).sum())
+        den += float(w.pow(2).sum())
+    assert (num / den) ** 0.5 <= tol
+
+
+ARMS = {"oracle": 1e-5, "torch_cuda": 1e-4}
+
+
+@pytest.mark.parametrize("arm", list(ARMS))
+def test_config2_resnet18_adamw_clip_fp32(arm):
+    import torchvision
+    torch.manual_seed(0)
+    base = workloads.BatchModel(torchvision.models.resnet18(num_classes=10))
+    g = torch.Generator().manual_seed(1)
+    batches = [[torch.randn(64, 3, 32, 32, generator=g), torch.randint(0, 10, (64,), generator=g)]
+               for _ in range(6)]
+    hp = dict(lr=1e-3, weight_decay=1e-2, foreach=False)
+    net_a, net_b = copy.deepcopy(base), copy.deepcopy(base)
+    port = looper_port.run_generic_port(
+        net_a, workloads.CrossEntropy(), torch.optim.AdamW(net_a.parameters(), **hp), batches,
+        accum=1, max_norm=1.0, device="cuda",
+        optimizer_impl="oracle" if arm == "oracle" else "torch")
+    mine = _engine_run(net_b, workloads.CrossEntropy(),
+                       torch.optim.AdamW(net_b.parameters(), **hp), batches, accum=1,
+                       max_norm=1.0)
+    _compare(mine, port["params"], ARMS[arm])
+    # BatchNorm running statistics went through the same forward passes
+    for (k, a), (_, b) in zip(net_a.named_buffers(), net_b.named_buffers()):
+        assert torch.equal(a.cpu(), b.cpu()), k
+
+
+@pytest.mark.parametrize("arm", list(ARMS))
+def test_config3_resnet50_bf16_sgd_momentum(arm):
+    import torchvision
+    torch.manual_seed(0)
+    base = workloads.BatchModel(torchvision.models.resnet50())
+    g = torch.Generator().manual_seed(2)
+    batches = [[torch.randn(8, 3, 224, 224, generator=g), torch.randint(0, 1000, (8,), generator=g)]
+               for _ in range(4)]
+    hp = dict(lr=0.05, momentum=0.9, weight_decay=1e-4, foreach=False)
+    net_a, net_b = copy.deepcopy(base), copy.deepcopy(base)
+    port = looper_port.run_generic_port(
+        net_a, workloads.CrossEntropy(), torch.optim.SGD(net_a.parameters(), **hp), batches,
+        accum=1, max_norm=None, device="cuda", autocast_dtype=torch.bfloat16,
+        optimizer_impl="oracle" if arm == "oracle" else "torch")
+    mine = _engine_run(net_b, workloads.CrossEntropy(), torch.optim.SGD(net_b.parameters(), **hp),
+                       batches, accum=1, max_norm=None, mixed_precision="bf16")
+    _compare(mine, port["params"], ARMS[arm], exact=(arm == "oracle"))
+
+
+@pytest.mark.parametrize("arm", list(ARMS))
+def test_config4_gpt2_accum4_adamw_clip_bf16(arm):
+    from transformers import GPT2Config, GPT2LMHeadModel
+    torch.manual_seed(0)
+    cfg = GPT2Config(n_layer=2, n_head=4, n_embd=128, n_positions=64, vocab_size=1000,
+                     resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)
+    base = GPTBatch(GPT2LMHeadModel(cfg))
+    g = torch.Generator().manual_seed(3)
+    batches = [[torch.randint(0, 1000, (4, 64), generator=g)] for _ in range(12)]
+    hp = dict(lr=6e-4, betas=(0.9, 0.95), weight_decay=0.1, foreach=False)
+    net_a, net_b = copy.deepcopy(base), copy.deepcopy(base)
+    port = looper_port.run_generic_port(
+        net_a, NextToken(), torch.optim.AdamW(net_a.parameters(), **hp), batches, accum=4,
+        max_norm=1.0, device="cuda", autocast_dtype=torch.bfloat16,
+        optimizer_impl="oracle" if arm == "oracle" else "torch")
+    mine = _engine_run(net_b, NextToken(), torch.optim.AdamW(net_b.parameters(), **hp), batches,
+                       accum=4, max_norm=1.0, mixed_precision="bf16")
+    _compare(mine, port["params"], ARMS[arm])
