@@ -27,6 +27,7 @@ All arithmetic is torch's own (``torch.optim.*(foreach=False)``,
 """
 from __future__ import annotations
 
+import contextlib
 import time
 
 import torch
@@ -96,7 +97,8 @@ class OracleOptimizer:
 
 
 def train_epoch(net, objective, opt, sched, batches, *, accum: int, max_norm, device,
-                state: dict, world: int = 1, sync_loss: bool = True) -> None:
+                state: dict, world: int = 1, sync_loss: bool = True,
+                autocast_dtype=None) -> None:
     """One pass over ``batches`` (a sized iterable of CPU batches). Appends to ``state``:
     loss_steps/loss_values, lr_steps/lr_values; keeps the cross-epoch counters there."""
     net.train()
@@ -111,9 +113,15 @@ def train_epoch(net, objective, opt, sched, batches, *, accum: int, max_norm, de
         else:
             phase += 1
             sync = (phase % accum) == 0
+        # autocast is entered and left around every forward + objective, as Module.runner does
+        # (module.py:175-219): leaving the outermost context drops the cached low-precision
+        # weight copies, which would otherwise be stale after the optimizer step
+        amp = torch.autocast(device_type=torch.device(device).type, dtype=autocast_dtype) \
+            if autocast_dtype is not None else contextlib.nullcontext()
         with torch.enable_grad():
-            out = net(batch)
-            loss = objective(out)
+            with amp:
+                out = net(batch)
+                loss = objective(out)
             if sync_loss:
                 value += loss.item() / accum
             if sync:
@@ -238,15 +246,7 @@ def run_generic_port(net, objective, opt, batches, *, accum: int, max_norm, devi
                     for t in out]
         net.forward = forward
     state = new_state()
-    ctx = torch.autocast(device_type=torch.device(device).type, dtype=autocast_dtype) \
-        if autocast_dtype is not None else None
-    if ctx is not None:
-        ctx.__enter__()
-    try:
-        train_epoch(net, objective, opt, batches, sched=None, accum=accum, max_norm=max_norm,
-                    device=device, state=state)
-    finally:
-        if ctx is not None:
-            ctx.__exit__(None, None, None)
+    train_epoch(net, objective, opt, None, batches, accum=accum, max_norm=max_norm,
+                device=device, state=state, autocast_dtype=autocast_dtype)
     state["params"] = {k: p.detach().cpu().clone() for k, p in net.named_parameters()}
     return state
