@@ -48,6 +48,16 @@ ALGO_BYTES_STEP = 32      # AdamW update 28 B + grad zero-fill 4 B per fp32 para
 ALGO_BYTES_NORM = 4       # K1
 
 
+def measured_traffic():
+    """DRAM bytes per launch of the step kernel in this workload, from the committed ncu
+    --set full capture (profiles/r1_roofline.json); None if no capture is on record."""
+    p = ROOT / "profiles" / "r1_roofline.json"
+    try:
+        return json.loads(p.read_text())["resnet18_step_kernel"]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def peaks():
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -253,7 +263,11 @@ def run_ours(args) -> dict:
 
     host_ds = PoolDataset(pool=16 * BATCH, length=(W + K) * BATCH * world)
     probe2 = Probe(read_loss=True)
-    launcher2, _ = graph(rk.Dataset(host_ds, batch_size=BATCH, shuffle=False), probe2)
+    # an ordinary input pipeline: DataLoader kwargs pass straight through rocket.Dataset
+    launcher2, _ = graph(rk.Dataset(host_ds, batch_size=BATCH, shuffle=False,
+                                    num_workers=args.loader_workers,
+                                    prefetch_factor=4 if args.loader_workers else None),
+                         probe2)
     launcher2.launch()
     ms2 = torch.tensor([probe2.ms], device="cuda")
     if world > 1:
@@ -277,12 +291,13 @@ def run_ours(args) -> dict:
                    "params": n_params},
         "e2e": {"value": round(e2e_value, 1), "unit": "samples/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                "ms_per_step": round(float(ms2.item()) / K, 4)},
+                "ms_per_step": round(float(ms2.item()) / K, 4),
+                "loader_workers": args.loader_workers},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "rk_step_kernel<AdamOp> (fused AdamW+clip+zero)",
                      "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": None,
+                     "frac": round(achieved / peak, 4), "traffic": measured_traffic(),
                      "peak_source": peak_src, "algorithmic_bytes_per_param": ALGO_BYTES_STEP,
                      "launch_ms": round(k2_ms, 5),
                      "norm_kernel_ms": round(statistics.mean(norm_ms), 5) if norm_ms else None,
@@ -383,6 +398,8 @@ def main() -> None:
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-optstep", action="store_true", help="skip the 1e9-param microbench")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--loader-workers", type=int, default=4,
+                    help="DataLoader worker processes of the e2e leg (0 = load in-process)")
     args = ap.parse_args()
     if args.impl == "reference":
         out = run_reference(args)

@@ -42,6 +42,7 @@ typedef enum rk_status {
 /* ---- limits ---------------------------------------------------------------- */
 #define RK_MAX_GROUPS 64          /* optimizer param groups per launch           */
 #define RK_STEP_CHUNK 4096        /* elements per work chunk of the step kernels */
+#define RK_STEP_CHUNK_SMALL 1024  /* ... for tensor lists under 2^26 elements   */
 #define RK_NORM_CHUNK_MIN 4096    /* smallest chunk of the norm kernel           */
 
 /* ---- tensor list ----------------------------------------------------------- */

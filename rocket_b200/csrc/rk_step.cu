@@ -1,6 +1,6 @@
 // K2 / K3: fused multi-tensor optimizer steps (HBM-bound elementwise kernels).
 //
-// One persistent grid walks the step chunks (RK_STEP_CHUNK elements of one tensor) of
+// One persistent grid walks the step chunks (plan.chunk_step elements of one tensor) of
 // the whole tensor list; the chunk->tensor prefix table is staged in shared memory and
 // binary-searched per chunk.  Each thread keeps UNROLL 128-bit loads of every stream in
 // flight (p, g, m, v -> 16 independent LDG.128 for Adam) and writes p, m, v and the
@@ -18,7 +18,6 @@
 #include "rk_common.cuh"
 
 #define STEP_THREADS 256
-#define STEP_UNROLL 4  // 256 threads x 4 x float4 = 4096 elements = RK_STEP_CHUNK
 
 // ---- per-group constants, passed by value in kernel-parameter space ------------------
 struct AdamDev {
@@ -155,6 +154,7 @@ rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table tabl
   const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
   const int n_tensors = h->n_tensors;
   const int n_chunks = h->n_chunks_step;
+  const int chunk = h->chunk_step;
   const rk_tensor_desc* descs = reinterpret_cast<const rk_tensor_desc*>(plan + h->off_descs);
   const int32_t* prefix = rk_stage_prefix(
       reinterpret_cast<const int32_t*>(plan + h->off_prefix_step), n_tensors + 1, s_prefix);
@@ -172,9 +172,9 @@ rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table tabl
     Op op;
     op.h = table.g[d.group];
     if ((d.flags & RK_TENSOR_SKIP) || (op.h.flags & GROUP_SKIP)) continue;
-    const int64_t base = (int64_t)(c - prefix[t]) * RK_STEP_CHUNK;
+    const int64_t base = (int64_t)(c - prefix[t]) * chunk;
     const int64_t rem = d.numel - base;
-    const int count = rem < RK_STEP_CHUNK ? (int)rem : RK_STEP_CHUNK;
+    const int count = rem < chunk ? (int)rem : chunk;
     float* P = d.p + base;
     float* G = d.g + base;
     float* M = d.m + base;
