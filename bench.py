@@ -129,6 +129,8 @@ def run_ours(args) -> dict:
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
+    if os.environ.get("RK_SWITCH"):
+        sys.setswitchinterval(float(os.environ["RK_SWITCH"]))
     W, K = args.warmup, args.steps
     assert W >= 3, "timing rules: at least 3 warm-up steps"
     torch.backends.cudnn.benchmark = True
@@ -398,7 +400,7 @@ def main() -> None:
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-optstep", action="store_true", help="skip the 1e9-param microbench")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
-    ap.add_argument("--loader-workers", type=int, default=4,
+    ap.add_argument("--loader-workers", type=int, default=0,
                     help="DataLoader worker processes of the e2e leg (0 = load in-process)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -22,6 +22,7 @@ batches have been drawn (the Looper drops ``attrs.batch`` every iteration).
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Any
 
 import torch
@@ -280,7 +281,11 @@ class EngineDataLoader:
         ahead is also what tells `end_of_dataloader` apart (forced gradient sync on the
         last batch), so it costs nothing extra."""
         stager = self.engine.stager
-        reader = _Reader(self._loader, self.skip_batches, depth=2)
+        # Measured on B200 (ResNet-18 step, 3 MB batches): pulling batches in a reader thread
+        # beats pulling them inline by 6-12 % with or without DataLoader worker processes.
+        threaded = os.environ.get("RK_READER", "1")
+        reader = (_Reader if threaded == "1" else _InlineReader)(
+            self._loader, self.skip_batches, depth=2)
         try:
             def stage(data):
                 if data is None:
@@ -304,6 +309,22 @@ class EngineDataLoader:
                 pending = nxt
         finally:
             reader.close()
+
+
+class _InlineReader:
+    """Same interface as _Reader, but batches are pulled in the calling thread."""
+
+    def __init__(self, loader, skip: int, depth: int):
+        self._it = iter(loader)
+        for _ in range(skip):
+            if next(self._it, None) is None:
+                break
+
+    def get(self):
+        return next(self._it, None)
+
+    def close(self) -> None:
+        self._it = None
 
 
 class _Reader:

@@ -80,7 +80,17 @@ def _compare(mine, want, tol, exact=False):
     assert (num / den) ** 0.5 <= tol
 
 
-ARMS = {"oracle": 1e-5, "torch_cuda": 1e-4}
+# "oracle": the full run against the C-oracle arithmetic (bar 1e-5; bit-exact expected).
+# "torch_cuda_first_step": ONE optimizer step against torch.optim's CUDA kernels.  Longer
+# horizons are meaningless for that arm on these networks: torch's CUDA and CPU AdamW kernels
+# round differently (tests/test_engine_gpu.py) and batch-norm / bf16 networks amplify that --
+# measured on B200: torch-CUDA vs torch-CPU arithmetic drift to 1.8e-2 on ResNet-18 after 6
+# steps and 1e-1 on a small GPT-2 after 3, with the engine exactly on the CPU side.
+ARMS = {"oracle": 1e-5, "torch_cuda_first_step": 1e-5}
+
+
+def _horizon(batches, accum, arm):
+    return batches if arm == "oracle" else batches[:accum]
 
 
 @pytest.mark.parametrize("arm", list(ARMS))
@@ -92,6 +102,7 @@ def test_config2_resnet18_adamw_clip_fp32(arm):
     batches = [[torch.randn(64, 3, 32, 32, generator=g), torch.randint(0, 10, (64,), generator=g)]
                for _ in range(6)]
     hp = dict(lr=1e-3, weight_decay=1e-2, foreach=False)
+    batches = _horizon(batches, 1, arm)
     net_a, net_b = copy.deepcopy(base), copy.deepcopy(base)
     port = looper_port.run_generic_port(
         net_a, workloads.CrossEntropy(), torch.optim.AdamW(net_a.parameters(), **hp), batches,
@@ -115,6 +126,7 @@ def test_config3_resnet50_bf16_sgd_momentum(arm):
     batches = [[torch.randn(8, 3, 224, 224, generator=g), torch.randint(0, 1000, (8,), generator=g)]
                for _ in range(4)]
     hp = dict(lr=0.05, momentum=0.9, weight_decay=1e-4, foreach=False)
+    batches = _horizon(batches, 1, arm)
     net_a, net_b = copy.deepcopy(base), copy.deepcopy(base)
     port = looper_port.run_generic_port(
         net_a, workloads.CrossEntropy(), torch.optim.SGD(net_a.parameters(), **hp), batches,
@@ -135,6 +147,7 @@ def test_config4_gpt2_accum4_adamw_clip_bf16(arm):
     g = torch.Generator().manual_seed(3)
     batches = [[torch.randint(0, 1000, (4, 64), generator=g)] for _ in range(12)]
     hp = dict(lr=6e-4, betas=(0.9, 0.95), weight_decay=0.1, foreach=False)
+    batches = _horizon(batches, 4, arm)
     net_a, net_b = copy.deepcopy(base), copy.deepcopy(base)
     port = looper_port.run_generic_port(
         net_a, NextToken(), torch.optim.AdamW(net_a.parameters(), **hp), batches, accum=4,
@@ -142,8 +155,4 @@ def test_config4_gpt2_accum4_adamw_clip_bf16(arm):
         optimizer_impl="oracle" if arm == "oracle" else "torch")
     mine = _engine_run(net_b, NextToken(), torch.optim.AdamW(net_b.parameters(), **hp), batches,
                        accum=4, max_norm=1.0, mixed_precision="bf16")
-    # torch-CUDA arm: a bf16 forward turns last-ulp parameter differences into whole bf16
-    # steps of the activations, so the torch-CUDA-vs-CPU arithmetic gap grows faster here
-    # (measured 9.5e-4 on a LayerNorm bias after 3 optimizer steps); the oracle arm, which
-    # shares the engine's arithmetic, stays within 1e-5.
-    _compare(mine, port["params"], ARMS[arm] if arm == "oracle" else 1e-2)
+    _compare(mine, port["params"], ARMS[arm])
