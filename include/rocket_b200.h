@@ -147,6 +147,11 @@ int rk_l2norm_multi(const void* plan_host, const void* plan_dev, float grad_scal
 int rk_l2norm_multi_static(const void* plan_host, const void* plan_dev, float grad_scale,
                            float* total_norm_dev, float* tensor_norms_dev, void* stream);
 
+/* Level 2 of K1 on its own: per-tensor norms and the total from per-chunk partials that are
+ * already in scratch (rk_comm_allreduce_norm writes them).  Same fixed-order reduction.   */
+int rk_l2norm_finalize(const void* plan_host, const void* plan_dev, void* scratch_dev,
+                       float* total_norm_dev, float* tensor_norms_dev, void* stream);
+
 /* ---- K2: fused multi-tensor Adam / AdamW step ---------------------------------
  * One pass over HBM doing, per element and in this order:
  *   g  = g * grad_scale                      (1/world_size; skipped when 1.0)
@@ -194,6 +199,32 @@ int rk_meter_argmax_count(const void* logits, int dtype, const int64_t* labels,
  * the .item() sync.                                                               */
 int rk_scalar_accumulate(const float* value_dev, double divisor, double* acc_dev,
                          void* stream);
+
+/* ---- K6: gradient all-reduce over NVLink peer memory, fused with 1/W and the norm ------------
+ * Replaces what the reference gets from torch DDP (rocket/core/module.py:106 ->
+ * accelerator.prepare -> DistributedDataParallel: $TORCH/nn/parallel/distributed.py, C++
+ * reducer + ncclAllReduce per 25 MiB bucket) and the separate norm pass of clip_grad_norm_.
+ * Every rank owns one device "arena" that all ranks of the node have mapped (CUDA IPC; the
+ * host side does the mapping):   [ signal pad: RK_COMM_SIGNAL_BYTES | norm scratch | gradients ]
+ * arenas[q] is rank q's arena as mapped in THIS process (arenas[rank] is the local one);
+ * scratch_offset is where the norm scratch starts inside every arena.  The gradient pointers
+ * in the plan must point into the local arena; the same offsets are used on the peers.
+ * rk_comm_allreduce_norm reduces the norm chunks [chunk_lo, chunk_hi) of the plan (a bucket):
+ * afterwards every rank holds sum_r(g_r) * (1/W) in place, bit-identical everywhere, and the
+ * chunks' sum-of-squares partials in its scratch; rk_l2norm_finalize turns them into the
+ * norm.  All ranks must call it with the same arguments in the same order; each rank's
+ * kernel waits for its peers' (flags with a per-bucket epoch, no resets), so every rank's
+ * launch must be able to run concurrently with the others' -- one GPU per rank.
+ * world in {2, 4, 8}; bucket < RK_COMM_MAX_BUCKETS; max_ctas <= 0 means one CTA per SM.    */
+#define RK_COMM_MAX_WORLD 8
+#define RK_COMM_MAX_BUCKETS 256
+#define RK_COMM_SIGNAL_BYTES 36864
+typedef struct rk_comm rk_comm;
+int rk_comm_create(rk_comm** out, int rank, int world, void* const* arenas,
+                   uint64_t scratch_offset);
+int rk_comm_allreduce_norm(rk_comm* comm, const void* plan_host, const void* plan_dev,
+                           int chunk_lo, int chunk_hi, int bucket, int max_ctas, void* stream);
+int rk_comm_destroy(rk_comm* comm);
 
 /* ---- K5: pinned-ring batch stager ---------------------------------------------------
  * Replaces the blocking pageable `Tensor.to(device)` of rocket/utils/torch.py:50-51

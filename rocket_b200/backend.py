@@ -31,7 +31,8 @@ class TensorSpec:
 class Plan:
     """Tensor-list metadata for the multi-tensor kernels: host blob, device copy, scratch."""
 
-    def __init__(self, specs: list[TensorSpec], device: torch.device):
+    def __init__(self, specs: list[TensorSpec], device: torch.device,
+                 scratch: torch.Tensor | None = None):
         lib = N.load()
         self.specs = specs
         self.n = len(specs)
@@ -55,7 +56,17 @@ class Plan:
         N.check(lib.rk_plan_build(descs, self.n, self.host.data_ptr(), plan_bytes.value),
                 "rk_plan_build")
         self.dev = self.host.to(device, non_blocking=False)
-        self.scratch = torch.zeros(scratch_bytes.value, dtype=torch.uint8, device=device)
+        if scratch is None:
+            scratch = torch.zeros(scratch_bytes.value, dtype=torch.uint8, device=device)
+        elif scratch.numel() < scratch_bytes.value:
+            raise ValueError(f"scratch of {scratch.numel()} bytes, plan needs {scratch_bytes.value}")
+        self.scratch = scratch
+        # header fields the host side needs (struct rk_plan_header, csrc/rk_common.cuh):
+        # int32[3] = chunk_norm, int32[5] = n_chunks_norm, uint32[8] = off_prefix_norm
+        words = self.host.numpy().view("<i4")
+        self.chunk_norm, self.n_chunks_norm = int(words[3]), int(words[5])
+        off = int(words[8]) // 4
+        self.prefix_norm = words[off:off + self.n + 1].copy()
         self.total_norm = torch.zeros(1, dtype=torch.float32, device=device)
         self.tensor_norms = torch.zeros(self.n, dtype=torch.float32, device=device)
         self.numel = sum(s.p.numel() for s in specs)
@@ -76,8 +87,43 @@ class NativeBackend:
     def _stream() -> int:
         return torch.cuda.current_stream().cuda_stream
 
-    def make_plan(self, specs: list[TensorSpec]) -> Plan:
-        return Plan(specs, self.device)
+    def make_plan(self, specs: list[TensorSpec], scratch: torch.Tensor | None = None) -> Plan:
+        return Plan(specs, self.device, scratch)
+
+    @staticmethod
+    def scratch_bytes(numels: list[int]) -> int:
+        lib = N.load()
+        arr = (ctypes.c_int64 * len(numels))(*numels)
+        pb, sb = ctypes.c_size_t(), ctypes.c_size_t()
+        N.check(lib.rk_plan_query(arr, len(numels), ctypes.byref(pb), ctypes.byref(sb)),
+                "rk_plan_query")
+        return sb.value
+
+    # K1, level 2 only: partials are already in plan.scratch (written by the fused all-reduce)
+    def l2norm_finalize(self, plan: Plan, want_tensor_norms: bool = False):
+        N.check(self.lib.rk_l2norm_finalize(
+            plan.host.data_ptr(), plan.dev.data_ptr(), plan.scratch.data_ptr(),
+            plan.total_norm.data_ptr(),
+            plan.tensor_norms.data_ptr() if want_tensor_norms else None, self._stream()),
+            "rk_l2norm_finalize")
+        return plan.total_norm
+
+    # K6
+    def comm_create(self, rank: int, world: int, arena_ptrs: list[int], scratch_offset: int):
+        handle = ctypes.c_void_p()
+        arr = (ctypes.c_void_p * world)(*arena_ptrs)
+        N.check(self.lib.rk_comm_create(ctypes.byref(handle), rank, world, arr, scratch_offset),
+                "rk_comm_create")
+        return handle
+
+    def comm_allreduce_norm(self, comm, plan: Plan, chunk_lo: int, chunk_hi: int, bucket: int,
+                            max_ctas: int, stream: int) -> None:
+        N.check(self.lib.rk_comm_allreduce_norm(comm, plan.host.data_ptr(), plan.dev.data_ptr(),
+                                                chunk_lo, chunk_hi, bucket, max_ctas, stream),
+                "rk_comm_allreduce_norm")
+
+    def comm_destroy(self, comm) -> None:
+        self.lib.rk_comm_destroy(comm)
 
     # K1
     def l2norm(self, plan: Plan, grad_scale: float = 1.0, want_tensor_norms: bool = False):

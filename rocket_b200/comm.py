@@ -4,29 +4,43 @@ The reference gets this implicitly: ``accelerator.prepare(module)`` wraps the mo
 DDP (reference rocket/core/module.py:106), whose C++ reducer copies every gradient into
 25 MiB buckets (dividing by the world size), all-reduces each bucket as backward fills it,
 and copies the result back.  Here gradients already live in the optimizer's flat buffer
-(rocket_b200/flat.py), so a bucket is just a contiguous slice of it:
+(rocket_b200/flat.py), so a bucket is a contiguous slice of it and nothing is copied in or out.
+Two implementations share the bucketing and the hook logic:
 
-* no copy-in, no copy-out -- NCCL reduces the gradient memory in place;
-* plain SUM on the wire (lets NVSwitch reduce in-network); the 1/world_size factor is
-  folded into the norm and step kernels' gradient read (``grad_scale``), which is exact for
-  power-of-two world sizes and therefore identical to DDP's divide-then-sum;
-* buckets are launched from ``post_accumulate_grad`` hooks in reverse parameter order, on
-  NCCL's own stream, so the exchange overlaps the rest of backward; on accumulation
-  micro-steps the hooks do nothing (DDP ``no_sync`` semantics);
-* after the exchange every rank holds bit-identical gradients, so the deterministic norm
-  kernel yields bit-identical clip coefficients with no further collective.
+``P2PGradSync`` (default on one node of NVLink-connected GPUs)
+    One hand-written kernel per bucket and rank (csrc/rk_comm.cu) that does the whole
+    exchange over NVLink peer memory: every rank reduces the chunks it owns by loading them
+    from all peers, scales by 1/world_size, writes the result back into every peer's buffer
+    and, in the same pass, produces the sum-of-squares partials of the global gradient norm
+    (so clipping needs no separate pass over the gradients).  Launched on a side stream from
+    ``post_accumulate_grad`` hooks, it overlaps the rest of backward.
+
+``GradSync`` (NCCL; used across nodes, on CPU/gloo in tests, or with ROCKET_B200_GRAD_SYNC=nccl)
+    In-place ``all_reduce(SUM)`` of each bucket on NCCL's stream; the 1/world_size factor is
+    folded into the norm and step kernels' gradient read (``grad_scale``), which is exact for
+    power-of-two world sizes and therefore identical to DDP's divide-then-sum.
+
+Both: buckets are issued in reverse parameter order as their last gradient arrives; on
+accumulation micro-steps the hooks do nothing (DDP ``no_sync`` semantics); after the exchange
+every rank holds bit-identical gradients, so the deterministic norm yields bit-identical
+clip coefficients with no further collective.
 """
 from __future__ import annotations
+
+import os
 
 import torch
 import torch.distributed as dist
 
 
-class GradSync:
-    def __init__(self, opt, engine, bucket_cap_mb: float = 32.0, first_bucket_mb: float = 1.0):
+class _BucketedSync:
+    """Bucketing over the flat gradient buffer + readiness hooks (shared by both backends)."""
+
+    def __init__(self, opt, engine, bucket_cap_mb: float, first_bucket_mb: float = 1.0):
         self.opt = opt
         self.engine = engine
-        self.buckets: list[tuple[int, int]] = []       # element ranges of flat_g
+        self.param_ranges: list[tuple[int, int]] = []   # [first_param, last_param] inclusive
+        self.buckets: list[tuple[int, int]] = []        # element ranges of flat_g
         self.bucket_of: list[int] = [0] * len(opt._params)
         self._members: list[list[int]] = []
         cap = int(first_bucket_mb * (1 << 20)) // 4
@@ -42,13 +56,14 @@ class GradSync:
                 lo = opt._offsets[i]
                 b = len(self.buckets)
                 self.buckets.append((lo, hi))
+                self.param_ranges.append((i, members[0]))
                 self._members.append(members)
                 for m in members:
                     self.bucket_of[m] = b
                 hi, members, size, cap = lo, [], 0, big
         self._pending = [len(m) for m in self._members]
         self._launched = [False] * len(self.buckets)
-        self._works: list = []
+        self._finished = False
         self._handles = [p.register_post_accumulate_grad_hook(self._make_hook(i))
                          for i, p in enumerate(opt._params)]
         self.bytes_reduced = 0
@@ -57,13 +72,58 @@ class GradSync:
         def hook(param):
             if not self.engine.sync_gradients or not self.opt._adopted[i]:
                 return
-            if param.grad.data_ptr() != self.opt._grad_ptr[i]:
-                return                      # adopted later, reduced in finish()
+            if param.grad.data_ptr() != self.opt._grad_ptr[i] or not self._can_launch():
+                return                      # reduced later, from finish()
             b = self.bucket_of[i]
             self._pending[b] -= 1
             if self._pending[b] == 0:
                 self._launch(b)
         return hook
+
+    def _can_launch(self) -> bool:
+        return True
+
+    def _launch(self, b: int) -> None:
+        raise NotImplementedError
+
+    def _wait(self) -> None:
+        raise NotImplementedError
+
+    #: factor the norm / step kernels still have to apply when they read a gradient
+    grad_scale = 1.0
+    #: True when finish() leaves the norm's per-chunk partials in the plan's scratch
+    fused_norm = False
+
+    def finish(self) -> bool:
+        """Launch whatever backward did not, then order the current stream after all of it.
+        Idempotent within a step; ``step_done`` re-arms it."""
+        if not self._finished:
+            # every rank must issue the buckets in the same order: leftovers go by index
+            for b in range(len(self.buckets)):
+                if not self._launched[b]:
+                    self._launch(b)
+            self._wait()
+            self._finished = True
+        return self.fused_norm
+
+    def step_done(self) -> None:
+        self._pending = [len(m) for m in self._members]
+        self._launched = [False] * len(self.buckets)
+        self._finished = False
+
+    def remove(self) -> None:
+        for h in self._handles:
+            h.remove()
+        self._handles = []
+
+
+class GradSync(_BucketedSync):
+    """NCCL (or gloo) in-place SUM all-reduce per bucket."""
+
+    def __init__(self, opt, engine, bucket_cap_mb: float = 32.0):
+        super().__init__(opt, engine, bucket_cap_mb)
+        self._works: list = []
+        self.grad_scale = 1.0 / engine.num_processes
 
     def _launch(self, b: int) -> None:
         lo, hi = self.buckets[b]
@@ -72,22 +132,96 @@ class GradSync:
         self._launched[b] = True
         self.bytes_reduced += (hi - lo) * 4
 
-    def finish(self) -> None:
-        """Launch whatever backward did not, then order the current stream after all of it."""
-        # buckets must be issued in the same order on every rank: launch leftovers by index
-        for b in range(len(self.buckets)):
-            if not self._launched[b]:
-                self._launch(b)
+    def _wait(self) -> None:
         for w in self._works:
             w.wait()
         self._works.clear()
-        self._pending = [len(m) for m in self._members]
-        self._launched = [False] * len(self.buckets)
+
+
+class P2PGradSync(_BucketedSync):
+    """Fused all-reduce + 1/W + norm partials over NVLink peer memory (csrc/rk_comm.cu)."""
+
+    fused_norm = True
+    grad_scale = 1.0           # the kernel already wrote averaged gradients
+
+    def __init__(self, opt, engine, bucket_cap_mb: float = 32.0):
+        super().__init__(opt, engine, bucket_cap_mb)
+        if len(self.buckets) > 256:
+            raise NotImplementedError("more than 256 gradient buckets")
+        self.backend = engine.backend
+        self.max_ctas = int(os.environ.get("ROCKET_B200_COMM_CTAS", "0"))
+        self.stream = torch.cuda.Stream(device=engine.device)
+        self._event = torch.cuda.Event()
+        self._peers = self._map_peers(opt.arena, engine)
+        self._comm = self.backend.comm_create(
+            engine.process_index, engine.num_processes, [t.data_ptr() for t in self._peers],
+            opt._scratch_offset)
+        dist.barrier()         # every rank has mapped every arena (and they are zero-filled)
+
+    @staticmethod
+    def _map_peers(arena: torch.Tensor, engine) -> list[torch.Tensor]:
+        """Exchange CUDA IPC handles of the arenas (torch's own IPC plumbing) and map the
+        peers' arenas into this process, on THIS rank's device so that peer access is enabled
+        towards it."""
+        from torch.multiprocessing import reductions
+        torch.cuda.synchronize(engine.device)
+        _, meta = reductions.reduce_tensor(arena)
+        metas = [None] * engine.num_processes
+        dist.all_gather_object(metas, meta)
+        peers = []
+        for q, m in enumerate(metas):
+            if q == engine.process_index:
+                peers.append(arena)
+                continue
+            m = list(m)
+            m[6] = engine.device.index          # open the handle in our own context
+            peers.append(reductions.rebuild_cuda_tensor(*m))
+        return peers
+
+    def _can_launch(self) -> bool:
+        return self.opt._plan is not None
+
+    def _chunk_range(self, b: int) -> tuple[int, int]:
+        first, last = self.param_ranges[b]
+        prefix = self.opt._plan.prefix_norm
+        return int(prefix[first]), int(prefix[last + 1])
+
+    def _launch(self, b: int) -> None:
+        plan = self.opt._get_plan()
+        lo, hi = self._chunk_range(b)
+        # the comm stream starts this bucket once the gradients produced so far are final
+        self._event.record(torch.cuda.current_stream(self.engine.device))
+        self.stream.wait_event(self._event)
+        self.backend.comm_allreduce_norm(self._comm, plan, lo, hi, b, self.max_ctas,
+                                         self.stream.cuda_stream)
+        self._launched[b] = True
+        e0, e1 = self.buckets[b]
+        self.bytes_reduced += (e1 - e0) * 4
+
+    def _wait(self) -> None:
+        torch.cuda.current_stream(self.engine.device).wait_stream(self.stream)
 
     def remove(self) -> None:
-        for h in self._handles:
-            h.remove()
-        self._handles = []
+        super().remove()
+        if self._comm is not None:
+            torch.cuda.synchronize(self.engine.device)
+            dist.barrier()     # nobody unmaps while a peer may still be writing
+            self.backend.comm_destroy(self._comm)
+            self._comm = None
+            self._peers = []
+
+
+def p2p_possible(engine) -> bool:
+    """Fused NVLink path: CUDA, one node, 2/4/8 ranks, every pair of devices peer-accessible."""
+    if engine.device.type != "cuda" or engine.num_processes not in (2, 4, 8):
+        return False
+    if os.environ.get("ROCKET_B200_GRAD_SYNC", "p2p") != "p2p":
+        return False
+    if int(os.environ.get("LOCAL_WORLD_SIZE", engine.num_processes)) != engine.num_processes:
+        return False
+    me = engine.device.index
+    return all(q == me or torch.cuda.can_device_access_peer(me, q)
+               for q in range(engine.num_processes))
 
 
 def broadcast_module_state(module: torch.nn.Module, src: int = 0) -> None:

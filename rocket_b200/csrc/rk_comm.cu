@@ -1,0 +1,264 @@
+// K6: gradient exchange fused with the 1/world_size scale and the norm's first level,
+// over NVLink peer memory.  One kernel per bucket, per rank:
+//
+//   start barrier   every rank tells every peer "my gradients of this bucket are final"
+//   reduce + write  rank r owns the norm chunks c with c % W == r.  For each it loads the
+//                   chunk from all W ranks' gradient buffers (P2P loads over NVLink), sums
+//                   them in rank order, scales by 1/W, accumulates the sum of squares, and
+//                   stores the averaged chunk into all W buffers (P2P stores).  The chunk's
+//                   sum of squares goes into every rank's norm scratch.
+//   end barrier     "all my stores have landed" to every peer; wait for the same from them.
+//
+// Compared with copy-in / ncclAllReduce / copy-out + a separate norm pass: the gradients
+// cross HBM once on the owner (read) and once everywhere (write), the wire carries the same
+// 2(W-1)/W bytes per element as a ring, the 4 B/param norm pass disappears, and because each
+// element is reduced by exactly one rank, in a fixed order, all replicas end up with
+// bit-identical gradients and bit-identical norm partials.
+//
+// Memory: every rank owns one "arena" allocation [signals | norm scratch | gradients] that
+// all peers have mapped (CUDA IPC, done by the host side); peers.arena[q] is rank q's arena
+// as seen from this rank.  Cross-GPU flags carry a monotonically increasing epoch, so they
+// never need resetting.
+#include "rk_common.cuh"
+
+#define COMM_THREADS 256
+#define COMM_WARPS (COMM_THREADS / 32)
+#define COMM_UNROLL 2
+
+struct CommPeers {
+  char* arena[RK_COMM_MAX_WORLD];
+};
+
+struct CommSignals {
+  unsigned long long ready[RK_COMM_MAX_BUCKETS][RK_COMM_MAX_WORLD];
+  unsigned long long done[RK_COMM_MAX_BUCKETS][RK_COMM_MAX_WORLD];
+  unsigned int arrived[RK_COMM_MAX_BUCKETS];
+};
+static_assert(sizeof(CommSignals) <= RK_COMM_SIGNAL_BYTES, "signal pad too small");
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_peer4(float* p, const float4& v) {
+  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+template <int W>
+__global__ void __launch_bounds__(COMM_THREADS)
+rk_allreduce_norm_kernel(const CommPeers peers, int rank, const char* __restrict__ plan,
+                         unsigned long long scratch_off, int chunk_lo, int chunk_hi, int bucket,
+                         float scale, unsigned long long epoch) {
+  __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
+  __shared__ double s_red[2][COMM_WARPS];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  CommSignals* mine = reinterpret_cast<CommSignals*>(peers.arena[rank]);
+
+  // ---- start barrier ---------------------------------------------------------------
+  if (blockIdx.x == 0 && tid < W)
+    st_release_sys(&reinterpret_cast<CommSignals*>(peers.arena[tid])->ready[bucket][rank], epoch);
+
+  const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
+  const int n_tensors = h->n_tensors;
+  const int chunk = h->chunk_norm;
+  const rk_tensor_desc* descs = reinterpret_cast<const rk_tensor_desc*>(plan + h->off_descs);
+  const int32_t* prefix = rk_stage_prefix(
+      reinterpret_cast<const int32_t*>(plan + h->off_prefix_norm), n_tensors + 1, s_prefix);
+
+  if (tid < W) {
+    while (ld_acquire_sys(&mine->ready[bucket][tid]) < epoch) { }
+  }
+  __syncthreads();
+
+  // ---- owned chunks: c in [chunk_lo, chunk_hi), c % W == rank -------------------------
+  int first = chunk_lo + ((rank - chunk_lo % W) + W) % W;
+  int parity = 0;
+  for (int c = first + (int)blockIdx.x * W; c < chunk_hi; c += (int)gridDim.x * W, parity ^= 1) {
+    const int t = rk_find_tensor(prefix, n_tensors, c);
+    const rk_tensor_desc d = descs[t];
+    const int64_t base = (int64_t)(c - prefix[t]) * chunk;
+    const int64_t rem = d.numel - base;
+    const int count = rem < chunk ? (int)rem : chunk;
+    if (!(d.flags & RK_TENSOR_SKIP)) {
+      const unsigned long long off =
+          (unsigned long long)(reinterpret_cast<char*>(d.g + base) - peers.arena[rank]);
+      float* g[W];
+#pragma unroll
+      for (int q = 0; q < W; ++q) g[q] = reinterpret_cast<float*>(peers.arena[q] + off);
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      if ((off & 15) == 0) {
+        const int nvec = count >> 2;
+        for (int i0 = tid; i0 < nvec; i0 += COMM_THREADS * COMM_UNROLL) {
+          float4 x[COMM_UNROLL][W];
+#pragma unroll
+          for (int k = 0; k < COMM_UNROLL; ++k) {
+            const int i = i0 + k * COMM_THREADS;
+            if (i < nvec) {
+#pragma unroll
+              for (int q = 0; q < W; ++q) x[k][q] = ld_peer4(g[q] + 4 * i);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < COMM_UNROLL; ++k) {
+            const int i = i0 + k * COMM_THREADS;
+            if (i < nvec) {
+              float4 s = x[k][0];
+#pragma unroll
+              for (int q = 1; q < W; ++q) {   // fixed rank order: identical on every owner
+                s.x = __fadd_rn(s.x, x[k][q].x);
+                s.y = __fadd_rn(s.y, x[k][q].y);
+                s.z = __fadd_rn(s.z, x[k][q].z);
+                s.w = __fadd_rn(s.w, x[k][q].w);
+              }
+              s.x = __fmul_rn(s.x, scale); s.y = __fmul_rn(s.y, scale);
+              s.z = __fmul_rn(s.z, scale); s.w = __fmul_rn(s.w, scale);
+              a0 = fmaf(s.x, s.x, a0); a1 = fmaf(s.y, s.y, a1);
+              a2 = fmaf(s.z, s.z, a2); a3 = fmaf(s.w, s.w, a3);
+#pragma unroll
+              for (int q = 0; q < W; ++q) st_peer4(g[q] + 4 * i, s);
+            }
+          }
+        }
+        const int i = (nvec << 2) + tid;
+        if (i < count) {
+          float s = g[0][i];
+#pragma unroll
+          for (int q = 1; q < W; ++q) s = __fadd_rn(s, g[q][i]);
+          s = __fmul_rn(s, scale);
+          a0 = fmaf(s, s, a0);
+#pragma unroll
+          for (int q = 0; q < W; ++q) g[q][i] = s;
+        }
+      } else {
+        for (int i = tid; i < count; i += COMM_THREADS) {
+          float s = g[0][i];
+#pragma unroll
+          for (int q = 1; q < W; ++q) s = __fadd_rn(s, g[q][i]);
+          s = __fmul_rn(s, scale);
+          a0 = fmaf(s, s, a0);
+#pragma unroll
+          for (int q = 0; q < W; ++q) g[q][i] = s;
+        }
+      }
+      double sd = (double)a0 + (double)a1 + ((double)a2 + (double)a3);
+      sd = rk_warp_sum(sd);
+      if (lane == 0) s_red[parity][warp] = sd;
+    } else if (lane == 0) {
+      s_red[parity][warp] = 0.0;
+    }
+    __syncthreads();
+    if (tid < W) {   // one thread per destination rank publishes this chunk's partial
+      double tot = 0.0;
+#pragma unroll
+      for (int w = 0; w < COMM_WARPS; ++w) tot += s_red[parity][w];
+      double* partials =
+          reinterpret_cast<double*>(peers.arena[tid] + scratch_off + h->off_partials);
+      partials[c] = tot;
+    }
+  }
+
+  // ---- end barrier ---------------------------------------------------------------------
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned int prev = atomicAdd(&mine->arrived[bucket], 1u);
+    if (prev == gridDim.x - 1) {
+      mine->arrived[bucket] = 0u;
+      __threadfence_system();
+      for (int q = 0; q < W; ++q)
+        st_release_sys(&reinterpret_cast<CommSignals*>(peers.arena[q])->done[bucket][rank], epoch);
+      for (int q = 0; q < W; ++q)
+        while (ld_acquire_sys(&mine->done[bucket][q]) < epoch) { }
+      __threadfence_system();
+    }
+  }
+}
+
+struct rk_comm {
+  int rank, world, device, sms;
+  CommPeers peers;
+  unsigned long long scratch_off;
+  unsigned long long epoch[RK_COMM_MAX_BUCKETS];
+};
+
+extern "C" int rk_comm_create(rk_comm** out, int rank, int world, void* const* arenas,
+                              uint64_t scratch_offset) {
+  RK_REQUIRE(out && arenas, RK_ERR_INVALID, "rk_comm_create: null argument");
+  RK_REQUIRE(world == 2 || world == 4 || world == 8, RK_ERR_UNSUPPORTED,
+             "rk_comm_create: world size %d (supported: 2, 4, 8)", world);
+  RK_REQUIRE(rank >= 0 && rank < world, RK_ERR_INVALID, "rk_comm_create: rank %d of %d", rank, world);
+  RK_REQUIRE(scratch_offset >= RK_COMM_SIGNAL_BYTES && scratch_offset % 256 == 0, RK_ERR_INVALID,
+             "rk_comm_create: scratch must follow the %d-byte signal pad, 256-byte aligned",
+             RK_COMM_SIGNAL_BYTES);
+  rk_comm* c = new rk_comm();
+  c->rank = rank;
+  c->world = world;
+  c->scratch_off = scratch_offset;
+  for (int q = 0; q < RK_COMM_MAX_WORLD; ++q) c->peers.arena[q] = nullptr;
+  for (int q = 0; q < world; ++q) {
+    if (!arenas[q]) {
+      delete c;
+      RK_REQUIRE(false, RK_ERR_INVALID, "rk_comm_create: arena of rank %d is null", q);
+    }
+    c->peers.arena[q] = (char*)arenas[q];
+  }
+  for (int b = 0; b < RK_COMM_MAX_BUCKETS; ++b) c->epoch[b] = 0;
+  cudaError_t e = cudaGetDevice(&c->device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, c->device);
+  if (e != cudaSuccess) {
+    rk_set_error("rk_comm_create: %s", cudaGetErrorString(e));
+    delete c;
+    return (int)e;
+  }
+  *out = c;
+  return 0;
+}
+
+extern "C" int rk_comm_allreduce_norm(rk_comm* c, const void* plan_host, const void* plan_dev,
+                                      int chunk_lo, int chunk_hi, int bucket, int max_ctas,
+                                      void* stream) {
+  RK_REQUIRE(c && plan_host && plan_dev, RK_ERR_INVALID, "rk_comm_allreduce_norm: null argument");
+  const rk_plan_header* h = (const rk_plan_header*)plan_host;
+  RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "rk_comm_allreduce_norm: bad plan magic");
+  RK_REQUIRE(bucket >= 0 && bucket < RK_COMM_MAX_BUCKETS, RK_ERR_TOO_LARGE,
+             "rk_comm_allreduce_norm: bucket %d outside [0,%d)", bucket, RK_COMM_MAX_BUCKETS);
+  RK_REQUIRE(0 <= chunk_lo && chunk_lo <= chunk_hi && chunk_hi <= h->n_chunks_norm, RK_ERR_INVALID,
+             "rk_comm_allreduce_norm: chunk range [%d,%d) outside [0,%d]", chunk_lo, chunk_hi,
+             h->n_chunks_norm);
+  const int W = c->world;
+  const int owned = (chunk_hi - chunk_lo + W - 1) / W;
+  int grid = max_ctas > 0 ? max_ctas : c->sms;
+  if (grid > owned) grid = owned;
+  if (grid < 1) grid = 1;   // still takes part in both barriers
+  const unsigned long long epoch = ++c->epoch[bucket];
+  const float scale = 1.0f / (float)W;
+  cudaStream_t s = (cudaStream_t)stream;
+#define RK_LAUNCH(WW)                                                                        \
+  rk_allreduce_norm_kernel<WW><<<grid, COMM_THREADS, 0, s>>>(c->peers, c->rank,              \
+      (const char*)plan_dev, c->scratch_off, chunk_lo, chunk_hi, bucket, scale, epoch)
+  switch (W) {
+    case 2: RK_LAUNCH(2); break;
+    case 4: RK_LAUNCH(4); break;
+    case 8: RK_LAUNCH(8); break;
+  }
+#undef RK_LAUNCH
+  RK_CUDA(cudaGetLastError());
+  g_rk_launches.fetch_add(1);
+  return 0;
+}
+
+extern "C" int rk_comm_destroy(rk_comm* c) {
+  delete c;
+  return 0;
+}

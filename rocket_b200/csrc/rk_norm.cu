@@ -20,6 +20,71 @@ __device__ __forceinline__ float sq_acc(float acc, float x, float s) {
   return fmaf(y, y, acc);
 }
 
+// ---- level 2: partials -> per-tensor norms -> total norm, by ONE CTA, in a fixed order ----
+__device__ __forceinline__ void rk_norm_level2(const rk_plan_header* h,
+                                               const int32_t* __restrict__ gprefix,
+                                               const double* partials, float* tnorms,
+                                               char* scratch, float* total_out,
+                                               float* tnorm_out, unsigned int* ticket,
+                                               double (*s_red)[NORM_WARPS]) {
+  const int n_tensors = h->n_tensors;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // ---- level 2a: per-tensor norms, one warp per small tensor -----------------------
+  for (int t = warp; t < n_tensors; t += NORM_WARPS) {
+    const int c0 = gprefix[t], c1 = gprefix[t + 1];
+    if (c1 - c0 > NORM_BIG_TENSOR) continue;
+    double s = 0.0;
+    for (int c = c0 + lane; c < c1; c += 32) s += __ldcg(partials + c);
+    s = rk_warp_sum(s);
+    if (lane == 0) tnorms[t] = (float)sqrt(s);
+  }
+  // ---- level 2b: big tensors, whole CTA each ---------------------------------------
+  int par = 0;
+  for (int t = 0; t < n_tensors; ++t) {
+    const int c0 = gprefix[t], c1 = gprefix[t + 1];
+    if (c1 - c0 <= NORM_BIG_TENSOR) continue;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int c = c0 + tid;
+    for (; c + 3 * NORM_THREADS < c1; c += 4 * NORM_THREADS) {
+      s0 += __ldcg(partials + c);
+      s1 += __ldcg(partials + c + NORM_THREADS);
+      s2 += __ldcg(partials + c + 2 * NORM_THREADS);
+      s3 += __ldcg(partials + c + 3 * NORM_THREADS);
+    }
+    for (; c < c1; c += NORM_THREADS) s0 += __ldcg(partials + c);
+    double s = rk_warp_sum((s0 + s1) + (s2 + s3));
+    if (lane == 0) s_red[par][warp] = s;
+    __syncthreads();
+    if (tid == 0) {
+      double tot = 0.0;
+#pragma unroll
+      for (int w = 0; w < NORM_WARPS; ++w) tot += s_red[par][w];
+      tnorms[t] = (float)sqrt(tot);
+    }
+    par ^= 1;
+  }
+  __syncthreads();  // tnorms written by this CTA are visible to this CTA
+  // ---- level 2c: norm of the per-tensor norms (clip_grad.py:106-107) -----------------
+  double acc = 0.0;
+  for (int t = tid; t < n_tensors; t += NORM_THREADS) {
+    const float n = tnorms[t];
+    acc += (double)n * (double)n;
+    if (tnorm_out) tnorm_out[t] = n;
+  }
+  acc = rk_warp_sum(acc);
+  if (lane == 0) s_red[par][warp] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    double tot = 0.0;
+#pragma unroll
+    for (int w = 0; w < NORM_WARPS; ++w) tot += s_red[par][w];
+    const float total = (float)sqrt(tot);
+    *reinterpret_cast<float*>(scratch + h->off_total) = total;
+    if (total_out) *total_out = total;
+    *ticket = 0u;  // ready for the next launch
+  }
+}
+
 __global__ void __launch_bounds__(NORM_THREADS)
 rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restrict__ scratch,
                  float* __restrict__ total_out, float* __restrict__ tnorm_out) {
@@ -97,60 +162,34 @@ rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restri
   if (!s_last) return;
   __threadfence();
 
-  // ---- level 2a: per-tensor norms, one warp per small tensor -----------------------
-  for (int t = warp; t < n_tensors; t += NORM_WARPS) {
-    const int c0 = gprefix[t], c1 = gprefix[t + 1];
-    if (c1 - c0 > NORM_BIG_TENSOR) continue;
-    double s = 0.0;
-    for (int c = c0 + lane; c < c1; c += 32) s += __ldcg(partials + c);
-    s = rk_warp_sum(s);
-    if (lane == 0) tnorms[t] = (float)sqrt(s);
-  }
-  // ---- level 2b: big tensors, whole CTA each ---------------------------------------
-  int par = 0;
-  for (int t = 0; t < n_tensors; ++t) {
-    const int c0 = gprefix[t], c1 = gprefix[t + 1];
-    if (c1 - c0 <= NORM_BIG_TENSOR) continue;
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    int c = c0 + tid;
-    for (; c + 3 * NORM_THREADS < c1; c += 4 * NORM_THREADS) {
-      s0 += __ldcg(partials + c);
-      s1 += __ldcg(partials + c + NORM_THREADS);
-      s2 += __ldcg(partials + c + 2 * NORM_THREADS);
-      s3 += __ldcg(partials + c + 3 * NORM_THREADS);
-    }
-    for (; c < c1; c += NORM_THREADS) s0 += __ldcg(partials + c);
-    double s = rk_warp_sum((s0 + s1) + (s2 + s3));
-    if (lane == 0) s_red[par][warp] = s;
-    __syncthreads();
-    if (tid == 0) {
-      double tot = 0.0;
-#pragma unroll
-      for (int w = 0; w < NORM_WARPS; ++w) tot += s_red[par][w];
-      tnorms[t] = (float)sqrt(tot);
-    }
-    par ^= 1;
-  }
-  __syncthreads();  // tnorms written by this CTA are visible to this CTA
-  // ---- level 2c: norm of the per-tensor norms (clip_grad.py:106-107) -----------------
-  double acc = 0.0;
-  for (int t = tid; t < n_tensors; t += NORM_THREADS) {
-    const float n = tnorms[t];
-    acc += (double)n * (double)n;
-    if (tnorm_out) tnorm_out[t] = n;
-  }
-  acc = rk_warp_sum(acc);
-  if (lane == 0) s_red[par][warp] = acc;
-  __syncthreads();
-  if (tid == 0) {
-    double tot = 0.0;
-#pragma unroll
-    for (int w = 0; w < NORM_WARPS; ++w) tot += s_red[par][w];
-    const float total = (float)sqrt(tot);
-    *reinterpret_cast<float*>(scratch + h->off_total) = total;
-    if (total_out) *total_out = total;
-    *ticket = 0u;  // ready for the next launch
-  }
+  rk_norm_level2(h, gprefix, partials, tnorms, scratch, total_out, tnorm_out, ticket, s_red);
+}
+
+// Level 2 on its own: for partials produced elsewhere (the fused all-reduce kernel writes
+// them, rk_comm.cu).  One CTA.
+__global__ void __launch_bounds__(NORM_THREADS)
+rk_l2norm_finalize_kernel(const char* __restrict__ plan, char* __restrict__ scratch,
+                          float* __restrict__ total_out, float* __restrict__ tnorm_out) {
+  __shared__ double s_red[2][NORM_WARPS];
+  const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
+  const int32_t* gprefix = reinterpret_cast<const int32_t*>(plan + h->off_prefix_norm);
+  rk_norm_level2(h, gprefix, reinterpret_cast<const double*>(scratch + h->off_partials),
+                 reinterpret_cast<float*>(scratch + h->off_tnorms), scratch, total_out,
+                 tnorm_out, reinterpret_cast<unsigned int*>(scratch + h->off_ticket), s_red);
+}
+
+extern "C" int rk_l2norm_finalize(const void* plan_host, const void* plan_dev,
+                                  void* scratch_dev, float* total_norm_dev,
+                                  float* tensor_norms_dev, void* stream) {
+  RK_REQUIRE(plan_host && plan_dev && scratch_dev, RK_ERR_INVALID,
+             "rk_l2norm_finalize: null plan or scratch");
+  const rk_plan_header* h = (const rk_plan_header*)plan_host;
+  RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "rk_l2norm_finalize: bad plan magic");
+  rk_l2norm_finalize_kernel<<<1, NORM_THREADS, 0, (cudaStream_t)stream>>>(
+      (const char*)plan_dev, (char*)scratch_dev, total_norm_dev, tensor_norms_dev);
+  RK_CUDA(cudaGetLastError());
+  g_rk_launches.fetch_add(1);
+  return 0;
 }
 
 extern "C" int rk_l2norm_multi(const void* plan_host, const void* plan_dev, float grad_scale,

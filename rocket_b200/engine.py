@@ -25,7 +25,8 @@ import torch
 import torch.distributed as dist
 
 from rocket_b200 import tracking
-from rocket_b200.comm import BufferSync, GradSync, broadcast_module_state
+from rocket_b200.comm import (BufferSync, GradSync, P2PGradSync, broadcast_module_state,
+                              p2p_possible)
 from rocket_b200.deferred import DeferredScalar
 from rocket_b200.flat import EngineOptimizer
 from rocket_b200.staging import EngineDataLoader, PinnedRingStager
@@ -166,6 +167,7 @@ class Engine:
         self._grad_sync: dict = {}
         self._buffer_sync: list = []
         self._bucket_cap_mb = bucket_cap_mb
+        self._p2p = None
         self.stager = None
         if self.device.type == "cuda" and stage_batches:
             self.stager = PinnedRingStager(self.device, slots=stage_slots,
@@ -199,7 +201,8 @@ class Engine:
         if isinstance(obj, torch.optim.Optimizer):
             opt = EngineOptimizer(obj, self)
             if self.num_processes > 1:
-                self._grad_sync[id(opt)] = GradSync(opt, self, self._bucket_cap_mb)
+                cls = P2PGradSync if opt.arena is not None else GradSync
+                self._grad_sync[id(opt)] = cls(opt, self, self._bucket_cap_mb)
             self._optimizers.append(opt)
             return opt
         if isinstance(obj, torch.optim.lr_scheduler.LRScheduler):
@@ -274,15 +277,34 @@ class Engine:
         (loss / self._accum_steps).backward(**kwargs)
 
     # ---- gradient exchange -----------------------------------------------------------------------------
-    def grad_scale(self) -> float:
-        """Factor the kernels apply when they read a gradient: 1/world_size, because the
-        wire reduction is a plain SUM."""
-        return 1.0 / self.num_processes
+    def wants_p2p(self) -> bool:
+        """Use the fused NVLink all-reduce kernel (comm.P2PGradSync) for gradient exchange?"""
+        if self._p2p is None:
+            self._p2p = hasattr(self.backend, "comm_create") and p2p_possible(self)
+            if self.num_processes > 1:           # all ranks must take the same path
+                flag = torch.tensor([int(self._p2p)], device=self.device)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                self._p2p = bool(flag.item())
+        return self._p2p
 
-    def finish_grad_sync(self, opt) -> None:
+    def grad_scale(self, opt=None) -> float:
+        """Factor the kernels still apply when they read a gradient: 1/world_size after a
+        plain SUM on the wire (NCCL path), 1 when the exchange kernel already averaged."""
+        sync = self._grad_sync.get(id(opt)) if opt is not None else None
+        if sync is not None:
+            return sync.grad_scale
+        return 1.0 / self.num_processes if opt is None else 1.0
+
+    def finish_grad_sync(self, opt) -> bool:
+        """Complete the gradient exchange of this step.  True if it also left the norm's
+        per-chunk partials in the plan's scratch (fused path)."""
+        sync = self._grad_sync.get(id(opt))
+        return sync.finish() if sync is not None else False
+
+    def grad_sync_step_done(self, opt) -> None:
         sync = self._grad_sync.get(id(opt))
         if sync is not None:
-            sync.finish()
+            sync.step_done()
 
     def note_late_gradient(self, opt) -> None:
         """A gradient was adopted into the flat buffer after backward: its bucket has not

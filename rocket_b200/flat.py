@@ -84,7 +84,20 @@ class EngineOptimizer:
             raise ValueError("optimizer has no trainable parameters")
         self._total = off
         self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
-        self.flat_g = torch.zeros(off, dtype=torch.float32, device=dev)
+        # Gradients live in an "arena" when the fused NVLink all-reduce will be used: one
+        # allocation [signal pad | norm scratch | gradients] that the peer ranks map (comm.py).
+        self.arena = self._scratch_view = None
+        if self.engine.wants_p2p():
+            from rocket_b200 import _native as N
+            sig = N.RK_COMM_SIGNAL_BYTES
+            scratch = -(-self.engine.backend.scratch_bytes([p.numel() for p in self._params])
+                        // 256) * 256
+            self.arena = torch.zeros(sig + scratch + 4 * off, dtype=torch.uint8, device=dev)
+            self._scratch_offset = sig
+            self._scratch_view = self.arena[sig:sig + scratch]
+            self.flat_g = self.arena[sig + scratch:].view(torch.float32)
+        else:
+            self.flat_g = torch.zeros(off, dtype=torch.float32, device=dev)
         self._needs_m = self._kind != "sgd" or any(
             g.get("momentum", 0) != 0 for g in self.optimizer.param_groups)
         self.flat_m = torch.zeros(off, dtype=torch.float32, device=dev) if self._needs_m else None
@@ -160,7 +173,11 @@ class EngineOptimizer:
         """Engine-level ``clip_grad_norm_``: computes the global norm now (one kernel) and
         applies the coefficient inside the next fused step.  Returns the device norm."""
         self._adopt_grads()
-        norm = self.engine.backend.l2norm(self._get_plan(), self.engine.grad_scale())
+        plan = self._get_plan()
+        if self.engine.finish_grad_sync(self):
+            norm = self.engine.backend.l2norm_finalize(plan)
+        else:
+            norm = self.engine.backend.l2norm(plan, self.engine.grad_scale(self))
         self._pending_clip = float(max_norm)
         self.last_grad_norm = norm
         return norm
@@ -172,14 +189,18 @@ class EngineOptimizer:
         if not eng.sync_gradients:
             return
         self._adopt_grads()
-        eng.finish_grad_sync(self)
         plan = self._get_plan()
-        scale = eng.grad_scale()
+        fused_norm = eng.finish_grad_sync(self)      # True: norm partials are in plan.scratch
+        scale = eng.grad_scale(self)
         max_norm = self._pending_clip if self._pending_clip is not None else self.max_grad_norm
         norm = None
         if max_norm is not None:
-            norm = self.last_grad_norm if self._pending_clip is not None \
-                else eng.backend.l2norm(plan, scale)
+            if self._pending_clip is not None:
+                norm = self.last_grad_norm
+            elif fused_norm:
+                norm = eng.backend.l2norm_finalize(plan)
+            else:
+                norm = eng.backend.l2norm(plan, scale)
             self.last_grad_norm = norm
         self._pending_clip = None
         active = set(self._group_of[i] for i in range(len(self._params)) if self._adopted[i])
@@ -204,6 +225,7 @@ class EngineOptimizer:
                                    skip=skip))
         fn = eng.backend.sgd_step if self._kind == "sgd" else eng.backend.adam_step
         fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)
+        eng.grad_sync_step_done(self)
         self._zeroed_by_step = True
         self._state_dirty = True
         self.optimizer._opt_called = True   # what torch's LRScheduler checks before warning
@@ -244,7 +266,10 @@ class EngineOptimizer:
                                 v=self._views_v[i].reshape(-1) if self.flat_v is not None else None,
                                 group=self._group_of[i], skip=not self._adopted[i])
                      for i in range(len(self._params))]
-            self._plan = self.engine.backend.make_plan(specs)
+            if self._scratch_view is not None:
+                self._plan = self.engine.backend.make_plan(specs, scratch=self._scratch_view)
+            else:
+                self._plan = self.engine.backend.make_plan(specs)
         return self._plan
 
     # ---- state in torch's own format (checkpoints) ----------------------------------------------------

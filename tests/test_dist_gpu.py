@@ -24,9 +24,11 @@ pytestmark = pytest.mark.gpu
 GOLDEN = Path(__file__).parent / "golden"
 
 
-def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str) -> None:
+def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str,
+                sync: str = "p2p") -> None:
     os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
-                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), TQDM_DISABLE="1")
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), TQDM_DISABLE="1",
+                      ROCKET_B200_GRAD_SYNC=sync)
     root = Path(__file__).resolve().parent.parent
     for p in (str(root), str(root / "tests")):
         if p not in sys.path:
@@ -43,7 +45,7 @@ def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str) -> No
         rk, tracker_backend=tracker, clip_via="kwarg" if kw["max_norm"] else "capsule",
         accuracy_cls=Accuracy, **kw)
     launcher.launch()
-    np.savez_compressed(Path(out_dir) / f"{case}_rank{rank}.npz",
+    np.savez_compressed(Path(out_dir) / f"{case}_{sync}_rank{rank}.npz",
                         **dist_worker._collect(h, tracker))
     import torch.distributed as dist
     if dist.is_initialized():
@@ -52,10 +54,11 @@ def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str) -> No
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 @pytest.mark.parametrize("case", list(dist_worker.WS2_CASES))
-def test_two_gpus_replicas_identical_and_track_reference(case, tmp_path):
-    port = 29800 + list(dist_worker.WS2_CASES).index(case)
-    mp.spawn(_gpu_worker, args=(2, port, case, str(tmp_path)), nprocs=2, join=True)
-    r0, r1 = (np.load(tmp_path / f"{case}_rank{r}.npz") for r in range(2))
+@pytest.mark.parametrize("sync", ["p2p", "nccl"])
+def test_two_gpus_replicas_identical_and_track_reference(case, sync, tmp_path):
+    port = 29800 + 2 * list(dist_worker.WS2_CASES).index(case) + (sync == "nccl")
+    mp.spawn(_gpu_worker, args=(2, port, case, str(tmp_path), sync), nprocs=2, join=True)
+    r0, r1 = (np.load(tmp_path / f"{case}_{sync}_rank{r}.npz") for r in range(2))
     gold = np.load(GOLDEN / f"{case}.npz")
     for k in gold.files:
         if k.startswith("param/"):
@@ -66,3 +69,21 @@ def test_two_gpus_replicas_identical_and_track_reference(case, tmp_path):
     np.testing.assert_allclose(r0["loss_values"], gold["loss_values"], rtol=1e-4)
     assert r0["accuracy_history"].tolist() == r1["accuracy_history"].tolist()
     assert np.abs(r0["accuracy_history"] - gold["accuracy_history"]).max() <= 2
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_fused_nvlink_allreduce_equals_nccl_path_bitwise(tmp_path):
+    """With two ranks a sum has one possible order, 1/2 is exact, and the fused kernel's norm
+    partials use the same chunking as the stand-alone norm kernel: the hand-written NVLink
+    exchange (+ fused norm) and the NCCL exchange (+ separate norm kernel) must therefore
+    produce bit-identical parameters, losses and counts."""
+    case = "ws2_adamw_clip"
+    for i, sync in enumerate(("p2p", "nccl")):
+        mp.spawn(_gpu_worker, args=(2, 29850 + i, case, str(tmp_path), sync), nprocs=2, join=True)
+    a = np.load(tmp_path / f"{case}_p2p_rank0.npz")
+    b = np.load(tmp_path / f"{case}_nccl_rank0.npz")
+    for k in a.files:
+        if k.startswith("param/"):
+            assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), k
+    assert a["loss_values"].tolist() == b["loss_values"].tolist()
+    assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
