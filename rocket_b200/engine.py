@@ -168,6 +168,7 @@ class Engine:
         self._buffer_sync: list = []
         self._bucket_cap_mb = bucket_cap_mb
         self._p2p = None
+        self.grad_sync_kinds: list[str] = []      # which exchange each optimizer got
         self.stager = None
         if self.device.type == "cuda" and stage_batches:
             self.stager = PinnedRingStager(self.device, slots=stage_slots,
@@ -203,6 +204,7 @@ class Engine:
             if self.num_processes > 1:
                 cls = P2PGradSync if opt.arena is not None else GradSync
                 self._grad_sync[id(opt)] = cls(opt, self, self._bucket_cap_mb)
+                self.grad_sync_kinds.append(cls.__name__)
             self._optimizers.append(opt)
             return opt
         if isinstance(obj, torch.optim.lr_scheduler.LRScheduler):

@@ -39,12 +39,18 @@ def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str,
     import workloads
     from rocket_b200.metrics import Accuracy
     from rocket_b200.tracking import MemoryTracker
+    from rocket_b200.engine import Engine
+    engines = []
+    rk.Launcher.engine_factory = staticmethod(lambda **k: engines.append(Engine(**k)) or engines[-1])
     tracker = MemoryTracker("memory")
     kw = dict(dist_worker.WS2_CASES[case])
     launcher, h = workloads.build_mnist_graph(
         rk, tracker_backend=tracker, clip_via="kwarg" if kw["max_norm"] else "capsule",
         accuracy_cls=Accuracy, **kw)
     launcher.launch()
+    # the path under test really ran (no silent fall back to the other exchange)
+    assert engines[0].grad_sync_kinds == ["P2PGradSync" if sync == "p2p" else "GradSync"], \
+        engines[0].grad_sync_kinds
     np.savez_compressed(Path(out_dir) / f"{case}_{sync}_rank{rank}.npz",
                         **dist_worker._collect(h, tracker))
     import torch.distributed as dist
