@@ -114,9 +114,34 @@ def make_resnet18():
     return workloads.BatchModel(torchvision.models.resnet18(num_classes=10))
 
 
+def make_resnet50():
+    import torchvision
+    import workloads
+    torch.manual_seed(0)
+    return workloads.BatchModel(torchvision.models.resnet50())
+
+
+# The default is the driver's headline workload (configs[1]).  `resnet50` is configs[2]
+# (ImageNet-shaped, bf16 autocast, SGD momentum) for the 1 -> 8 GPU scaling target.
+WORKLOADS = {
+    "resnet18": dict(
+        net=make_resnet18, shape=(3, 32, 32), classes=10, mixed_precision=None, max_norm=1.0,
+        opt=lambda ps: torch.optim.AdamW(ps, lr=1e-3, weight_decay=1e-2),
+        label="configs[1]: ResNet-18(num_classes=10), synthetic 3x32x32, bs=256/GPU, "
+              "AdamW(lr=1e-3,wd=1e-2)+clip 1.0, fp32, capsule API", dtype="f32"),
+    "resnet50": dict(
+        net=make_resnet50, shape=(3, 224, 224), classes=1000, mixed_precision="bf16",
+        max_norm=None, opt=lambda ps: torch.optim.SGD(ps, lr=0.1, momentum=0.9, weight_decay=1e-4),
+        label="configs[2]: ResNet-50, synthetic 3x224x224, bs=256/GPU, bf16 autocast, "
+              "SGD(momentum 0.9, wd 1e-4), capsule API", dtype="bf16 autocast / f32 master"),
+}
+WL = WORKLOADS["resnet18"]
+
+
 def synthetic_batch(rank: int, n: int = BATCH):
     g = torch.Generator().manual_seed(1234 + rank)
-    return torch.randn(n, 3, 32, 32, generator=g), torch.randint(0, 10, (n,), generator=g)
+    return (torch.randn(n, *WL["shape"], generator=g),
+            torch.randint(0, WL["classes"], (n,), generator=g))
 
 
 def run_ours(args) -> dict:
@@ -157,6 +182,12 @@ def run_ours(args) -> dict:
 
         def adam_step(self, *a, **k):
             return self._timed("step", super().adam_step, *a, **k)
+
+        def sgd_step(self, *a, **k):
+            return self._timed("step", super().sgd_step, *a, **k)
+
+        def l2norm_finalize(self, *a, **k):
+            return self._timed("norm", super().l2norm_finalize, *a, **k)
 
     holder = {}
 
@@ -224,13 +255,14 @@ def run_ours(args) -> dict:
                 self.ms = self.t0.elapsed_time(self.t1)
 
     def graph(data_capsule, probe):
-        net = make_resnet18()
-        opt = torch.optim.AdamW(net.parameters(), lr=1e-3, weight_decay=1e-2)
+        net = WL["net"]()
+        opt = WL["opt"](net.parameters())
         inner = [rk.Loss(objective=workloads.CrossEntropy()),
-                 rk.Optimizer(opt, max_grad_norm=1.0)]
+                 rk.Optimizer(opt, max_grad_norm=WL["max_norm"])]
         looper = rk.Looper([data_capsule, rk.Module(net, capsules=inner), probe],
                            tag="bench", repeats=W + K)
-        return rk.Launcher([looper], num_epochs=1, destroy_process_group_after_launch=False), opt
+        return rk.Launcher([looper], num_epochs=1, mixed_precision=WL["mixed_precision"],
+                           destroy_process_group_after_launch=False), opt
 
     # ---- leg 1: inputs resident in HBM -----------------------------------------------------------
     probe = Probe(read_loss=False)
@@ -252,8 +284,8 @@ def run_ours(args) -> dict:
         """(W+K)*world batches of host samples drawn from a fixed synthetic pool."""
         def __init__(self, pool: int, length: int):
             g = torch.Generator().manual_seed(99)
-            self.x = torch.randn(pool, 3, 32, 32, generator=g)
-            self.y = torch.randint(0, 10, (pool,), generator=g)
+            self.x = torch.randn(pool, *WL["shape"], generator=g)
+            self.y = torch.randint(0, WL["classes"], (pool,), generator=g)
             self.length = length
 
         def __len__(self):
@@ -263,7 +295,8 @@ def run_ours(args) -> dict:
             j = i % self.x.shape[0]
             return self.x[j], self.y[j]
 
-    host_ds = PoolDataset(pool=16 * BATCH, length=(W + K) * BATCH * world)
+    pool = 16 * BATCH if WL["shape"][-1] <= 64 else 2 * BATCH
+    host_ds = PoolDataset(pool=pool, length=(W + K) * BATCH * world)
     probe2 = Probe(read_loss=True)
     # an ordinary input pipeline: DataLoader kwargs pass straight through rocket.Dataset
     launcher2, _ = graph(rk.Dataset(host_ds, batch_size=BATCH, shuffle=False,
@@ -275,19 +308,20 @@ def run_ours(args) -> dict:
     if world > 1:
         dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
     e2e_value = world * BATCH * K / (float(ms2.item()) / 1e3)
-    h2d = BATCH * (3 * 32 * 32 * 4 + 8)
+    h2d = BATCH * (WL["shape"][0] * WL["shape"][1] * WL["shape"][2] * 4 + 8)
 
     peak, peak_src = peaks()
     k2_ms = statistics.mean(step_ms) if step_ms else float("nan")
-    achieved = ALGO_BYTES_STEP * n_params / (k2_ms * 1e-3) / 1e9
+    algo = ALGO_BYTES_STEP if args.workload == "resnet18" else 24   # SGD+momentum: 20 + 4
+    achieved = algo * n_params / (k2_ms * 1e-3) / 1e9
     out = {
         "metric": METRIC, "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": round(ms_total / K, 4),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": WL["dtype"],
         "data": "synthetic",
-        "config": {"workload": "configs[1]: ResNet-18(num_classes=10), synthetic 3x32x32, "
-                               "bs=256/GPU, AdamW(lr=1e-3,wd=1e-2)+clip 1.0, fp32, capsule API",
+        "config": {"workload": WL["label"],
                    "global_batch": BATCH * world, "parallelism": f"dp{world}",
+                   "grad_sync": (holder["engine"].grad_sync_kinds or ["none"])[0],
                    "l2": "no explicit flush: per-step working set (45 MB x4 optimizer streams "
                          "+ activations of bs 256) exceeds the 126 MB L2",
                    "params": n_params},
@@ -299,15 +333,16 @@ def run_ours(args) -> dict:
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "rk_step_kernel<AdamOp> (fused AdamW+clip+zero)",
                      "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": measured_traffic(),
-                     "peak_source": peak_src, "algorithmic_bytes_per_param": ALGO_BYTES_STEP,
+                     "frac": round(achieved / peak, 4),
+                     "traffic": measured_traffic() if args.workload == "resnet18" else None,
+                     "peak_source": peak_src, "algorithmic_bytes_per_param": algo,
                      "launch_ms": round(k2_ms, 5),
                      "norm_kernel_ms": round(statistics.mean(norm_ms), 5) if norm_ms else None,
                      "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
     }
     if rank == 0 and world == 1 and not args.no_optstep:
         out["optstep"] = optstep_microbench(peak)
-    if rank == 0 and world == 1 and not args.no_cpu:
+    if rank == 0 and world == 1 and not args.no_cpu and args.workload == "resnet18":
         out["cpu_baseline"] = cpu_port(budget_s=args.cpu_budget, threads=None, as_line=False)
     return out
 
@@ -400,9 +435,12 @@ def main() -> None:
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-optstep", action="store_true", help="skip the 1e9-param microbench")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--workload", default="resnet18", choices=list(WORKLOADS))
     ap.add_argument("--loader-workers", type=int, default=0,
                     help="DataLoader worker processes of the e2e leg (0 = load in-process)")
     args = ap.parse_args()
+    global WL
+    WL = WORKLOADS[args.workload]
     if args.impl == "reference":
         out = run_reference(args)
         if out:

@@ -209,6 +209,8 @@ class P2PGradSync(_BucketedSync):
             self.backend.comm_destroy(self._comm)
             self._comm = None
             self._peers = []
+            torch.cuda.ipc_collect()   # drop our mappings of the peers' arenas ...
+            dist.barrier()             # ... before any producer may free its arena
 
 
 def p2p_possible(engine) -> bool:

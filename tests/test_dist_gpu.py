@@ -93,3 +93,81 @@ def test_fused_nvlink_allreduce_equals_nccl_path_bitwise(tmp_path):
             assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), k
     assert a["loss_values"].tolist() == b["loss_values"].tolist()
     assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
+
+
+def _allreduce_worker(rank: int, world: int, port: int, out_dir: str) -> None:
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    root = Path(__file__).resolve().parent.parent
+    sys.path.insert(0, str(root))
+    import torch.distributed as dist
+    from rocket_b200 import _native as N
+    from rocket_b200.backend import NativeBackend, TensorSpec
+    from rocket_b200.comm import P2PGradSync
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    be = NativeBackend(dev)
+    sizes = [6, 10, 150, 4097, 48000, 1, 0, 123457, 3_000_001]       # awkward + multi-chunk
+    offs, total = [], 0
+    for n in sizes:
+        offs.append(total)
+        total += (n + 63) // 64 * 64
+    sig = N.RK_COMM_SIGNAL_BYTES
+    scratch = -(-be.scratch_bytes(sizes) // 256) * 256
+    arena = torch.zeros(sig + scratch + 4 * total, dtype=torch.uint8, device=dev)
+    flat = arena[sig + scratch:].view(torch.float32)
+    views = [flat[o:o + n] for o, n in zip(offs, sizes)]
+    specs = [TensorSpec(p=torch.zeros(n, device=dev), g=v, m=None, v=None, group=0)
+             for n, v in zip(sizes, views)]
+    plan = be.make_plan(specs, scratch=arena[sig:sig + scratch])
+
+    class Eng:
+        device, process_index, num_processes = dev, rank, world
+    peers = P2PGradSync._map_peers(arena, Eng)
+    comm = be.comm_create(rank, world, [t.data_ptr() for t in peers], sig)
+    dist.barrier()
+    stream = torch.cuda.current_stream().cuda_stream
+    half = plan.n_chunks_norm // 2
+    for it in range(3):                                 # epochs advance, nothing is reset
+        torch.manual_seed(100 * it + rank)
+        flat.normal_(0, 1e-2)
+        want = flat.clone()
+        dist.all_reduce(want)
+        want /= world
+        torch.cuda.synchronize()
+        dist.barrier()
+        be.comm_allreduce_norm(comm, plan, half, plan.n_chunks_norm, 0, 0, stream)   # two buckets
+        be.comm_allreduce_norm(comm, plan, 0, half, 1, 0, stream)
+        norm = be.l2norm_finalize(plan, want_tensor_norms=True).clone()
+        torch.cuda.synchronize()
+        got = flat.clone()
+        # replicas bit-identical
+        gathered = [torch.empty_like(got) for _ in range(world)]
+        dist.all_gather(gathered, got)
+        for q in range(world):
+            assert torch.equal(gathered[q], gathered[0]), (it, q)
+        # value: sum_r(g_r) / W up to fp32 summation order (exact for W == 2)
+        if world == 2:
+            assert torch.equal(got, want)
+        else:
+            assert torch.allclose(got, want, rtol=2e-6, atol=1e-9)
+        # fused norm partials == the stand-alone norm kernel on the averaged gradients
+        ref_plan = be.make_plan(specs)
+        ref = be.l2norm(ref_plan, 1.0, want_tensor_norms=True)
+        torch.cuda.synchronize()
+        assert torch.equal(norm, ref), (float(norm), float(ref))
+        assert torch.equal(plan.tensor_norms, ref_plan.tensor_norms)
+    dist.barrier()
+    be.comm_destroy(comm)
+    del peers
+    torch.cuda.ipc_collect()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_fused_allreduce_norm_kernel_against_nccl(world, tmp_path):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    mp.spawn(_allreduce_worker, args=(world, 29870 + world, str(tmp_path)), nprocs=world, join=True)
