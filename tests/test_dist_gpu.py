@@ -131,7 +131,9 @@ def _allreduce_worker(rank: int, world: int, port: int, out_dir: str) -> None:
     half = plan.n_chunks_norm // 2
     for it in range(3):                                 # epochs advance, nothing is reset
         torch.manual_seed(100 * it + rank)
-        flat.normal_(0, 1e-2)
+        flat.zero_()                                    # padding between tensors stays zero
+        for v in views:
+            v.normal_(0, 1e-2)
         want = flat.clone()
         dist.all_reduce(want)
         want /= world
