@@ -51,13 +51,15 @@ def _static_norm(plan, scale):
     dev = plan.dev.device
     total = torch.full((1,), -1.0, dtype=torch.float32, device=dev)
     per_tensor = torch.full((plan.n,), -1.0, dtype=torch.float32, device=dev)
-    before = torch.cuda.memory_allocated(dev)
+    # count torch's device allocations (not bytes in use: garbage left by earlier tests may be
+    # collected at any moment and would make a byte count move on its own)
+    before = torch.cuda.memory_stats(dev)["allocation.all.allocated"]
     rc = lib.rk_l2norm_multi_static(plan.host.data_ptr(), plan.dev.data_ptr(),
                                     ctypes.c_float(scale), total.data_ptr(),
                                     per_tensor.data_ptr(),
                                     torch.cuda.current_stream().cuda_stream)
     N.check(rc, "rk_l2norm_multi_static")
-    assert torch.cuda.memory_allocated(dev) == before        # torch's allocator untouched
+    assert torch.cuda.memory_stats(dev)["allocation.all.allocated"] == before   # none made
     torch.cuda.synchronize()
     return total.cpu().numpy(), per_tensor.cpu().numpy()
 
