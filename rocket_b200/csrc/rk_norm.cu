@@ -33,9 +33,18 @@ __device__ __forceinline__ void rk_norm_level2(const rk_plan_header* h,
   for (int t = warp; t < n_tensors; t += NORM_WARPS) {
     const int c0 = gprefix[t], c1 = gprefix[t + 1];
     if (c1 - c0 > NORM_BIG_TENSOR) continue;
-    double s = 0.0;
-    for (int c = c0 + lane; c < c1; c += 32) s += __ldcg(partials + c);
-    s = rk_warp_sum(s);
+    // four independent accumulators: four L2 loads in flight per lane (this loop is the
+    // serial tail of the kernel on small models)
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int c = c0 + lane;
+    for (; c + 96 < c1; c += 128) {
+      s0 += __ldcg(partials + c);
+      s1 += __ldcg(partials + c + 32);
+      s2 += __ldcg(partials + c + 64);
+      s3 += __ldcg(partials + c + 96);
+    }
+    for (; c < c1; c += 32) s0 += __ldcg(partials + c);
+    const double s = rk_warp_sum((s0 + s1) + (s2 + s3));
     if (lane == 0) tnorms[t] = (float)sqrt(s);
   }
   // ---- level 2b: big tensors, whole CTA each ---------------------------------------
@@ -104,6 +113,7 @@ rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restri
 
   const int32_t* prefix = rk_stage_prefix(gprefix, n_tensors + 1, s_prefix);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool stream_loads = h->total_numel > ((int64_t)16 << 20);   // > 64 MB of gradients
 
   int parity = 0;
   for (int c = blockIdx.x; c < n_chunks; c += gridDim.x, parity ^= 1) {
@@ -124,7 +134,10 @@ rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restri
 #pragma unroll
           for (int k = 0; k < NORM_UNROLL; ++k) {
             const int idx = i + k * NORM_THREADS;
-            x[k] = idx < nvec ? __ldcs(g4 + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+            // lists that fit in L2 are read again by the step kernel right away: keep them
+            // cached; larger ones are streamed (evict-first) so they do not thrash L2
+            x[k] = idx >= nvec ? make_float4(0.f, 0.f, 0.f, 0.f)
+                               : (stream_loads ? __ldcs(g4 + idx) : __ldg(g4 + idx));
           }
 #pragma unroll
           for (int k = 0; k < NORM_UNROLL; ++k) {

@@ -189,10 +189,12 @@ rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table tabl
         for (int k = 0; k < U; ++k) {
           const int i = i0 + k * STEP_THREADS;
           if (i < nvec) {
-            p4[k] = ldg4<HINT>(P + 4 * i);
-            g4[k] = ldg4<HINT>(G + 4 * i);
-            if (has_m) m4[k] = ldg4<HINT>(M + 4 * i);
-            if (Op::kHasV) v4[k] = ldg4<HINT>(V + 4 * i);
+            // HINT 3: the moments are touched once per step -> stream them past the caches;
+            // g was just read by the norm pass and p is read again by the next forward
+            p4[k] = ldg4<HINT == 3 ? 0 : HINT>(P + 4 * i);
+            g4[k] = ldg4<HINT == 3 ? 0 : HINT>(G + 4 * i);
+            if (has_m) m4[k] = ldg4<HINT == 3 ? 2 : HINT>(M + 4 * i);
+            if (Op::kHasV) v4[k] = ldg4<HINT == 3 ? 2 : HINT>(V + 4 * i);
           }
         }
 #pragma unroll
@@ -203,10 +205,11 @@ rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table tabl
             op(p4[k].y, prolog_g(g4[k].y, pr), m4[k].y, v4[k].y);
             op(p4[k].z, prolog_g(g4[k].z, pr), m4[k].z, v4[k].z);
             op(p4[k].w, prolog_g(g4[k].w, pr), m4[k].w, v4[k].w);
-            stg4<HINT>(P + 4 * i, p4[k]);
-            if (has_m) stg4<HINT>(M + 4 * i, m4[k]);
-            if (Op::kHasV) stg4<HINT>(V + 4 * i, v4[k]);
-            if (zero_grads) stg4<HINT>(G + 4 * i, make_float4(0.f, 0.f, 0.f, 0.f));
+            stg4<HINT == 3 ? 0 : HINT>(P + 4 * i, p4[k]);
+            if (has_m) stg4<HINT == 3 ? 2 : HINT>(M + 4 * i, m4[k]);
+            if (Op::kHasV) stg4<HINT == 3 ? 2 : HINT>(V + 4 * i, v4[k]);
+            if (zero_grads)
+              stg4<HINT == 3 ? 2 : HINT>(G + 4 * i, make_float4(0.f, 0.f, 0.f, 0.f));
           }
         }
       }
@@ -254,13 +257,20 @@ static int launch_variant(const rk_plan_header* h, const void* plan_dev, const T
 #ifndef RK_STEP_DEFAULT_VARIANT
 #define RK_STEP_DEFAULT_VARIANT 4
 #endif
-static int step_variant() {
-  static int v = -1;
-  if (v < 0) {
+#ifndef RK_STEP_SMALL_VARIANT
+#define RK_STEP_SMALL_VARIANT 9
+#endif
+// Lists that fit a few waves (a ResNet-18: 11M parameters, ~75 us) are latency- and
+// tail-bound: one load per stream in flight and twice the resident CTAs wins there
+// (66.5 us vs 76.2 us in the ResNet-18 step), while 2^26+ elements want U=2 / 3 CTAs per SM.
+static int step_variant(const rk_plan_header* h) {
+  static int forced = -2;
+  if (forced == -2) {
     const char* e = getenv("RK_STEP_VARIANT");
-    v = e ? atoi(e) : RK_STEP_DEFAULT_VARIANT;
+    forced = e ? atoi(e) : -1;
   }
-  return v;
+  if (forced >= 0) return forced;
+  return h->total_numel >= ((int64_t)1 << 26) ? RK_STEP_DEFAULT_VARIANT : RK_STEP_SMALL_VARIANT;
 }
 
 template <class Op, class Table>
@@ -287,7 +297,7 @@ static int launch_step(const void* plan_host, const void* plan_dev, const Table&
 #define RK_V(U, MINB, HINT)                                                              \
   rc = launch_variant<Op, Table, U, MINB, HINT>(h, plan_dev, table, total_norm_dev,      \
                                                 max_norm, grad_scale, zero_grads, stream)
-  switch (step_variant()) {
+  switch (step_variant(h)) {
     default:
     case 0: RK_V(4, 2, 0); break;
     case 1: RK_V(2, 4, 0); break;
@@ -304,6 +314,8 @@ static int launch_step(const void* plan_host, const void* plan_dev, const Table&
     case 12: RK_V(2, 3, 2); break;
     case 13: RK_V(2, 3, 1); break;
     case 14: RK_V(3, 3, 0); break;
+    case 15: RK_V(2, 3, 3); break;
+    case 16: RK_V(1, 6, 3); break;
   }
 #undef RK_V
   if (rc) return rc;
