@@ -123,7 +123,39 @@ def make_resnet50():
 
 # The default is the driver's headline workload (configs[1]).  `resnet50` is configs[2]
 # (ImageNet-shaped, bf16 autocast, SGD momentum) for the 1 -> 8 GPU scaling target.
+def make_gpt2():
+    import torch.nn.functional as F
+    from transformers import GPT2Config, GPT2LMHeadModel
+    torch.manual_seed(0)
+    lm = GPT2LMHeadModel(GPT2Config(resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0))
+
+    class GPT(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.lm = lm
+
+        def forward(self, batch):
+            ids = batch[0]
+            logits = self.lm(input_ids=ids).logits
+            return ids, ids, logits      # (inputs, targets, logits) like the image workloads
+    return GPT()
+
+
+class NextTokenLoss(torch.nn.Module):
+    def forward(self, batch):
+        ids, logits = batch[0], batch[2]
+        return torch.nn.functional.cross_entropy(
+            logits[:, :-1].reshape(-1, logits.shape[-1]).float(), ids[:, 1:].reshape(-1))
+
+
 WORKLOADS = {
+    "gpt2": dict(
+        net=make_gpt2, shape=(1024,), classes=50257, mixed_precision="bf16", max_norm=1.0,
+        batch=8, accum=4, tokens=True,
+        opt=lambda ps: torch.optim.AdamW(ps, lr=6e-4, betas=(0.9, 0.95), weight_decay=0.1),
+        label="configs[3]: GPT-2 small 124M (GPT2LMHeadModel), synthetic tokens seq 1024, "
+              "micro-batch 8/GPU, grad-accum 4, AdamW(6e-4,(0.9,0.95),wd 0.1)+clip 1.0, bf16 "
+              "autocast, capsule API", dtype="bf16 autocast / f32 master"),
     "resnet18": dict(
         net=make_resnet18, shape=(3, 32, 32), classes=10, mixed_precision=None, max_norm=1.0,
         opt=lambda ps: torch.optim.AdamW(ps, lr=1e-3, weight_decay=1e-2),
@@ -138,8 +170,12 @@ WORKLOADS = {
 WL = WORKLOADS["resnet18"]
 
 
-def synthetic_batch(rank: int, n: int = BATCH):
+def synthetic_batch(rank: int, n: int | None = None):
+    n = n or WL.get("batch", BATCH)
     g = torch.Generator().manual_seed(1234 + rank)
+    if WL.get("tokens"):
+        ids = torch.randint(0, WL["classes"], (n, *WL["shape"]), generator=g)
+        return ids, ids[:, 0].clone()
     return (torch.randn(n, *WL["shape"], generator=g),
             torch.randint(0, WL["classes"], (n,), generator=g))
 
@@ -241,6 +277,9 @@ def run_ours(args) -> dict:
                 self._fence()
                 self.launch0 = _native.launch_count()
                 be.timing = True
+                for sync in self._accelerator._grad_sync.values():
+                    if hasattr(sync, "profile"):
+                        sync.profile, self.sync = True, sync
                 if rank == 0:
                     self.sampler.start()
                 self.t0.record()
@@ -250,6 +289,9 @@ def run_ours(args) -> dict:
                 self.t1.record()
                 self._fence()
                 be.timing = False
+                if getattr(self, "sync", None) is not None:
+                    self.sync.profile = False
+                    self.exchange = [(nb, a.elapsed_time(b)) for nb, a, b in self.sync.timings]
                 self.launches = _native.launch_count() - self.launch0
                 self.clocks = self.sampler.stop() if rank == 0 else None
                 self.ms = self.t0.elapsed_time(self.t1)
@@ -257,11 +299,13 @@ def run_ours(args) -> dict:
     def graph(data_capsule, probe):
         net = WL["net"]()
         opt = WL["opt"](net.parameters())
-        inner = [rk.Loss(objective=workloads.CrossEntropy()),
+        objective = NextTokenLoss() if WL.get("tokens") else workloads.CrossEntropy()
+        inner = [rk.Loss(objective=objective),
                  rk.Optimizer(opt, max_grad_norm=WL["max_norm"])]
         looper = rk.Looper([data_capsule, rk.Module(net, capsules=inner), probe],
                            tag="bench", repeats=W + K)
         return rk.Launcher([looper], num_epochs=1, mixed_precision=WL["mixed_precision"],
+                           gradient_accumulation_steps=WL.get("accum", 1),
                            destroy_process_group_after_launch=False), opt
 
     # ---- leg 1: inputs resident in HBM -----------------------------------------------------------
@@ -276,7 +320,7 @@ def run_ours(args) -> dict:
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
-    value = world * BATCH * K / (ms_total / 1e3)
+    value = world * WL.get("batch", BATCH) * K / (ms_total / 1e3)
     launches, clocks = probe.launches, probe.clocks
 
     # ---- leg 2: end to end, host batches through Dataset + stager ----------------------------------
@@ -284,8 +328,12 @@ def run_ours(args) -> dict:
         """(W+K)*world batches of host samples drawn from a fixed synthetic pool."""
         def __init__(self, pool: int, length: int):
             g = torch.Generator().manual_seed(99)
-            self.x = torch.randn(pool, *WL["shape"], generator=g)
-            self.y = torch.randint(0, WL["classes"], (pool,), generator=g)
+            if WL.get("tokens"):
+                self.x = torch.randint(0, WL["classes"], (pool, *WL["shape"]), generator=g)
+                self.y = self.x[:, 0].clone()
+            else:
+                self.x = torch.randn(pool, *WL["shape"], generator=g)
+                self.y = torch.randint(0, WL["classes"], (pool,), generator=g)
             self.length = length
 
         def __len__(self):
@@ -295,11 +343,12 @@ def run_ours(args) -> dict:
             j = i % self.x.shape[0]
             return self.x[j], self.y[j]
 
-    pool = 16 * BATCH if WL["shape"][-1] <= 64 else 2 * BATCH
-    host_ds = PoolDataset(pool=pool, length=(W + K) * BATCH * world)
+    B = WL.get("batch", BATCH)
+    pool = 16 * B if WL["shape"][-1] <= 64 or WL.get("tokens") else 2 * B
+    host_ds = PoolDataset(pool=pool, length=(W + K) * B * world)
     probe2 = Probe(read_loss=True)
     # an ordinary input pipeline: DataLoader kwargs pass straight through rocket.Dataset
-    launcher2, _ = graph(rk.Dataset(host_ds, batch_size=BATCH, shuffle=False,
+    launcher2, _ = graph(rk.Dataset(host_ds, batch_size=B, shuffle=False,
                                     num_workers=args.loader_workers,
                                     prefetch_factor=4 if args.loader_workers else None),
                          probe2)
@@ -307,12 +356,14 @@ def run_ours(args) -> dict:
     ms2 = torch.tensor([probe2.ms], device="cuda")
     if world > 1:
         dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-    e2e_value = world * BATCH * K / (float(ms2.item()) / 1e3)
-    h2d = BATCH * (WL["shape"][0] * WL["shape"][1] * WL["shape"][2] * 4 + 8)
+    e2e_value = world * B * K / (float(ms2.item()) / 1e3)
+    sample_bytes = 8 * WL["shape"][0] if WL.get("tokens") else \
+        4 * WL["shape"][0] * WL["shape"][1] * WL["shape"][2]
+    h2d = B * (sample_bytes + 8)
 
     peak, peak_src = peaks()
     k2_ms = statistics.mean(step_ms) if step_ms else float("nan")
-    algo = ALGO_BYTES_STEP if args.workload == "resnet18" else 24   # SGD+momentum: 20 + 4
+    algo = 24 if args.workload == "resnet50" else ALGO_BYTES_STEP   # SGD+momentum: 20 + 4
     achieved = algo * n_params / (k2_ms * 1e-3) / 1e9
     out = {
         "metric": METRIC, "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
@@ -320,7 +371,8 @@ def run_ours(args) -> dict:
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": WL["dtype"],
         "data": "synthetic",
         "config": {"workload": WL["label"],
-                   "global_batch": BATCH * world, "parallelism": f"dp{world}",
+                   "global_batch": WL.get("batch", BATCH) * world * WL.get("accum", 1),
+                   "parallelism": f"dp{world}",
                    "grad_sync": (holder["engine"].grad_sync_kinds or ["none"])[0],
                    "l2": "no explicit flush: per-step working set (45 MB x4 optimizer streams "
                          "+ activations of bs 256) exceeds the 126 MB L2",
@@ -340,6 +392,20 @@ def run_ours(args) -> dict:
                      "norm_kernel_ms": round(statistics.mean(norm_ms), 5) if norm_ms else None,
                      "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
     }
+    if world > 1 and getattr(probe, "exchange", None):
+        # K6, measured live: the fused NVLink all-reduce + 1/W + norm kernels of the timed region
+        nbytes = sum(nb for nb, _ in probe.exchange)
+        ms_x = sum(t for _, t in probe.exchange)
+        bus = 2 * (world - 1) / world * nbytes / (ms_x * 1e-3) / 1e9
+        out["exchange"] = {
+            "kernel": "rk_allreduce_norm_kernel (NVLink P2P all-reduce + 1/W + norm partials)",
+            "launches_per_step": round(len(probe.exchange) / K, 2),
+            "bytes_per_step": nbytes // K, "kernel_ms_per_step": round(ms_x / K, 4),
+            "bus_gbs": round(bus, 1), "nvlink_peak_gbs": 770.0,
+            "frac": round(bus / 770.0, 4),
+            "note": "bus GB/s = 2(W-1)/W x bytes / kernel time = bytes crossing NVLink per "
+                    "direction per GPU; peak = measured peer-copy bandwidth (B200_PROFILING.md); "
+                    "kernel time includes waiting for the slowest rank's backward"}
     if rank == 0 and world == 1 and not args.no_optstep:
         out["optstep"] = optstep_microbench(peak)
     if rank == 0 and world == 1 and not args.no_cpu and args.workload == "resnet18":

@@ -152,6 +152,8 @@ class P2PGradSync(_BucketedSync):
         self.max_ctas = int(os.environ.get("ROCKET_B200_COMM_CTAS", "0"))
         self.stream = torch.cuda.Stream(device=engine.device)
         self._event = torch.cuda.Event()
+        self.profile = False        # bench.py: bracket every exchange kernel with events
+        self.timings: list = []     # (bucket bytes, start event, end event) on self.stream
         self._peers = self._map_peers(opt.arena, engine)
         self._comm = self.backend.comm_create(
             engine.process_index, engine.num_processes, [t.data_ptr() for t in self._peers],
@@ -192,10 +194,16 @@ class P2PGradSync(_BucketedSync):
         # the comm stream starts this bucket once the gradients produced so far are final
         self._event.record(torch.cuda.current_stream(self.engine.device))
         self.stream.wait_event(self._event)
+        e0, e1 = self.buckets[b]
+        if self.profile:
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record(self.stream)
         self.backend.comm_allreduce_norm(self._comm, plan, lo, hi, b, self.max_ctas,
                                          self.stream.cuda_stream)
+        if self.profile:
+            t1.record(self.stream)
+            self.timings.append(((e1 - e0) * 4, t0, t1))
         self._launched[b] = True
-        e0, e1 = self.buckets[b]
         self.bytes_reduced += (e1 - e0) * 4
 
     def _wait(self) -> None:
