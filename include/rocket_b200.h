@@ -215,15 +215,19 @@ int rk_scalar_accumulate(const float* value_dev, double divisor, double* acc_dev
  * norm.  All ranks must call it with the same arguments in the same order; each rank's
  * kernel waits for its peers' (flags with a per-bucket epoch, no resets), so every rank's
  * launch must be able to run concurrently with the others' -- one GPU per rank.
- * world in {2, 4, 8}; bucket < RK_COMM_MAX_BUCKETS; max_ctas <= 0 means one CTA per SM.    */
+ * world in {2, 4, 8}; bucket < RK_COMM_MAX_BUCKETS; max_ctas <= 0 means one CTA per SM.
+ * multicast_arena (may be NULL): an NVSwitch multicast mapping of all W arenas.  With it and
+ * use_multicast != 0 the kernel reduces with multimem.ld_reduce and replicates with
+ * multimem.st (in-switch sum / broadcast) instead of W loads and W stores per element.      */
 #define RK_COMM_MAX_WORLD 8
 #define RK_COMM_MAX_BUCKETS 256
 #define RK_COMM_SIGNAL_BYTES 36864
 typedef struct rk_comm rk_comm;
 int rk_comm_create(rk_comm** out, int rank, int world, void* const* arenas,
-                   uint64_t scratch_offset);
+                   void* multicast_arena, uint64_t scratch_offset);
 int rk_comm_allreduce_norm(rk_comm* comm, const void* plan_host, const void* plan_dev,
-                           int chunk_lo, int chunk_hi, int bucket, int max_ctas, void* stream);
+                           int chunk_lo, int chunk_hi, int bucket, int max_ctas,
+                           int use_multicast, void* stream);
 int rk_comm_destroy(rk_comm* comm);
 
 /* ---- K5: pinned-ring batch stager ---------------------------------------------------

@@ -86,9 +86,10 @@ def load() -> ctypes.CDLL:
     lib.rk_stage_release.argtypes = [c_void_p, c_int, c_void_p]
     lib.rk_stage_destroy.argtypes = [c_void_p]
     lib.rk_l2norm_finalize.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
-    lib.rk_comm_create.argtypes = [POINTER(c_void_p), c_int, c_int, POINTER(c_void_p), c_uint64]
+    lib.rk_comm_create.argtypes = [POINTER(c_void_p), c_int, c_int, POINTER(c_void_p), c_void_p,
+                                   c_uint64]
     lib.rk_comm_allreduce_norm.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
-                                           c_int, c_void_p]
+                                           c_int, c_int, c_void_p]
     lib.rk_comm_destroy.argtypes = [c_void_p]
     for name in EXPORTS:
         fn = getattr(lib, name)          # AttributeError here = header/library mismatch

@@ -109,17 +109,19 @@ class NativeBackend:
         return plan.total_norm
 
     # K6
-    def comm_create(self, rank: int, world: int, arena_ptrs: list[int], scratch_offset: int):
+    def comm_create(self, rank: int, world: int, arena_ptrs: list[int], scratch_offset: int,
+                    multicast_ptr: int = 0):
         handle = ctypes.c_void_p()
         arr = (ctypes.c_void_p * world)(*arena_ptrs)
-        N.check(self.lib.rk_comm_create(ctypes.byref(handle), rank, world, arr, scratch_offset),
-                "rk_comm_create")
+        N.check(self.lib.rk_comm_create(ctypes.byref(handle), rank, world, arr,
+                                        multicast_ptr or None, scratch_offset), "rk_comm_create")
         return handle
 
     def comm_allreduce_norm(self, comm, plan: Plan, chunk_lo: int, chunk_hi: int, bucket: int,
-                            max_ctas: int, stream: int) -> None:
+                            max_ctas: int, stream: int, use_multicast: bool = True) -> None:
         N.check(self.lib.rk_comm_allreduce_norm(comm, plan.host.data_ptr(), plan.dev.data_ptr(),
-                                                chunk_lo, chunk_hi, bucket, max_ctas, stream),
+                                                chunk_lo, chunk_hi, bucket, max_ctas,
+                                                int(use_multicast), stream),
                 "rk_comm_allreduce_norm")
 
     def comm_destroy(self, comm) -> None:

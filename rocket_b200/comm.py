@@ -154,31 +154,15 @@ class P2PGradSync(_BucketedSync):
         self._event = torch.cuda.Event()
         self.profile = False        # bench.py: bracket every exchange kernel with events
         self.timings: list = []     # (bucket bytes, start event, end event) on self.stream
-        self._peers = self._map_peers(opt.arena, engine)
+        ptrs, self.multicast_ptr, self._peers = map_arena(opt.arena, engine)
+        # in-switch reduction moves ~G bytes per GPU instead of 2(W-1)/W * G: a win from W = 4
+        want_mc = os.environ.get("ROCKET_B200_MULTICAST", "auto")
+        self.use_multicast = bool(self.multicast_ptr) and (
+            want_mc == "1" or (want_mc == "auto" and engine.num_processes >= 4))
         self._comm = self.backend.comm_create(
-            engine.process_index, engine.num_processes, [t.data_ptr() for t in self._peers],
-            opt._scratch_offset)
+            engine.process_index, engine.num_processes, ptrs, opt._scratch_offset,
+            self.multicast_ptr)
         dist.barrier()         # every rank has mapped every arena (and they are zero-filled)
-
-    @staticmethod
-    def _map_peers(arena: torch.Tensor, engine) -> list[torch.Tensor]:
-        """Exchange CUDA IPC handles of the arenas (torch's own IPC plumbing) and map the
-        peers' arenas into this process, on THIS rank's device so that peer access is enabled
-        towards it."""
-        from torch.multiprocessing import reductions
-        torch.cuda.synchronize(engine.device)
-        _, meta = reductions.reduce_tensor(arena)
-        metas = [None] * engine.num_processes
-        dist.all_gather_object(metas, meta)
-        peers = []
-        for q, m in enumerate(metas):
-            if q == engine.process_index:
-                peers.append(arena)
-                continue
-            m = list(m)
-            m[6] = engine.device.index          # open the handle in our own context
-            peers.append(reductions.rebuild_cuda_tensor(*m))
-        return peers
 
     def _can_launch(self) -> bool:
         return self.opt._plan is not None
@@ -199,7 +183,7 @@ class P2PGradSync(_BucketedSync):
             t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             t0.record(self.stream)
         self.backend.comm_allreduce_norm(self._comm, plan, lo, hi, b, self.max_ctas,
-                                         self.stream.cuda_stream)
+                                         self.stream.cuda_stream, self.use_multicast)
         if self.profile:
             t1.record(self.stream)
             self.timings.append(((e1 - e0) * 4, t0, t1))
@@ -219,6 +203,53 @@ class P2PGradSync(_BucketedSync):
             self._peers = []
             torch.cuda.ipc_collect()   # drop our mappings of the peers' arenas ...
             dist.barrier()             # ... before any producer may free its arena
+
+
+def alloc_arena(nbytes: int, device: torch.device) -> torch.Tensor:
+    """Zero-filled device memory that peers can map.  Preferred: torch's symmetric-memory
+    allocator (CUDA VMM allocations that also get an NVSwitch multicast mapping); otherwise a
+    plain allocation shared through CUDA IPC."""
+    if os.environ.get("ROCKET_B200_ARENA", "symm") == "symm":
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            arena = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+            arena.zero_()
+            arena._rk_symm = True
+            return arena
+        except Exception:
+            pass
+    return torch.zeros(nbytes, dtype=torch.uint8, device=device)
+
+
+def map_arena(arena: torch.Tensor, engine):
+    """Collective.  Returns (pointers to every rank's arena as mapped here, multicast pointer
+    or 0, objects that keep the mappings alive)."""
+    world, rank = engine.num_processes, engine.process_index
+    symm = torch.tensor([int(getattr(arena, "_rk_symm", False))], device=engine.device)
+    dist.all_reduce(symm, op=dist.ReduceOp.MIN)
+    torch.cuda.synchronize(engine.device)
+    if symm.item():
+        import torch.distributed._symmetric_memory as symm_mem
+        hdl = symm_mem.rendezvous(arena, dist.group.WORLD)
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        assert ptrs[rank] == arena.data_ptr(), "symmetric memory handle does not match the arena"
+        mc = int(hdl.multicast_ptr) if hdl.has_multicast_support else 0
+        return ptrs, mc, [hdl]
+    # CUDA IPC through torch's tensor-sharing plumbing; the handle is opened on THIS rank's
+    # device so that peer access towards the owner is enabled
+    from torch.multiprocessing import reductions
+    _, meta = reductions.reduce_tensor(arena)
+    metas = [None] * world
+    dist.all_gather_object(metas, meta)
+    peers = []
+    for q, m in enumerate(metas):
+        if q == rank:
+            peers.append(arena)
+            continue
+        m = list(m)
+        m[6] = engine.device.index
+        peers.append(reductions.rebuild_cuda_tensor(*m))
+    return [t.data_ptr() for t in peers], 0, peers
 
 
 def p2p_possible(engine) -> bool:

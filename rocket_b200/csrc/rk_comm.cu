@@ -24,6 +24,7 @@
 #define COMM_THREADS 256
 #define COMM_WARPS (COMM_THREADS / 32)
 #define COMM_UNROLL 2
+#define COMM_UNROLL_MC 4
 
 struct CommPeers {
   char* arena[RK_COMM_MAX_WORLD];
@@ -55,11 +56,38 @@ __device__ __forceinline__ void st_peer4(float* p, const float4& v) {
                :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-template <int W>
+// NVSwitch multicast ("multimem"): one load that returns the SUM over every rank's copy of the
+// address, reduced inside the switch, and one store that the switch replicates to every rank.
+__device__ __forceinline__ float4 mc_ld_reduce4(const float* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+  return r;
+}
+__device__ __forceinline__ float mc_ld_reduce1(const float* mc) {
+  float r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];"
+               : "=f"(r) : "l"(mc) : "memory");
+  return r;
+}
+__device__ __forceinline__ void mc_st4(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void mc_st1(float* mc, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" :: "l"(mc), "f"(v) : "memory");
+}
+
+// MC = false: P2P loads/stores on the peers' mapped arenas.
+// MC = true : multimem.ld_reduce / multimem.st on the arenas' multicast mapping -- the switch
+//             does the W-way sum and the W-way replication, so each GPU sends and receives
+//             about G bytes instead of 2(W-1)/W * G (worth it from W = 4 up).
+template <int W, bool MC>
 __global__ void __launch_bounds__(COMM_THREADS)
-rk_allreduce_norm_kernel(const CommPeers peers, int rank, const char* __restrict__ plan,
-                         unsigned long long scratch_off, int chunk_lo, int chunk_hi, int bucket,
-                         float scale, unsigned long long epoch) {
+rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
+                         const char* __restrict__ plan, unsigned long long scratch_off,
+                         int chunk_lo, int chunk_hi, int bucket, float scale,
+                         unsigned long long epoch) {
   __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   __shared__ double s_red[2][COMM_WARPS];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -93,62 +121,100 @@ rk_allreduce_norm_kernel(const CommPeers peers, int rank, const char* __restrict
     if (!(d.flags & RK_TENSOR_SKIP)) {
       const unsigned long long off =
           (unsigned long long)(reinterpret_cast<char*>(d.g + base) - peers.arena[rank]);
-      float* g[W];
-#pragma unroll
-      for (int q = 0; q < W; ++q) g[q] = reinterpret_cast<float*>(peers.arena[q] + off);
       float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-      if ((off & 15) == 0) {
-        const int nvec = count >> 2;
-        for (int i0 = tid; i0 < nvec; i0 += COMM_THREADS * COMM_UNROLL) {
-          float4 x[COMM_UNROLL][W];
+      if constexpr (MC) {
+        float* m = reinterpret_cast<float*>(mc_arena + off);
+        if ((off & 15) == 0) {
+          const int nvec = count >> 2;
+          for (int i0 = tid; i0 < nvec; i0 += COMM_THREADS * COMM_UNROLL_MC) {
+            float4 s[COMM_UNROLL_MC];
 #pragma unroll
-          for (int k = 0; k < COMM_UNROLL; ++k) {
-            const int i = i0 + k * COMM_THREADS;
-            if (i < nvec) {
-#pragma unroll
-              for (int q = 0; q < W; ++q) x[k][q] = ld_peer4(g[q] + 4 * i);
+            for (int k = 0; k < COMM_UNROLL_MC; ++k) {
+              const int i = i0 + k * COMM_THREADS;
+              if (i < nvec) s[k] = mc_ld_reduce4(m + 4 * i);
             }
-          }
 #pragma unroll
-          for (int k = 0; k < COMM_UNROLL; ++k) {
-            const int i = i0 + k * COMM_THREADS;
-            if (i < nvec) {
-              float4 s = x[k][0];
-#pragma unroll
-              for (int q = 1; q < W; ++q) {   // fixed rank order: identical on every owner
-                s.x = __fadd_rn(s.x, x[k][q].x);
-                s.y = __fadd_rn(s.y, x[k][q].y);
-                s.z = __fadd_rn(s.z, x[k][q].z);
-                s.w = __fadd_rn(s.w, x[k][q].w);
+            for (int k = 0; k < COMM_UNROLL_MC; ++k) {
+              const int i = i0 + k * COMM_THREADS;
+              if (i < nvec) {
+                s[k].x = __fmul_rn(s[k].x, scale); s[k].y = __fmul_rn(s[k].y, scale);
+                s[k].z = __fmul_rn(s[k].z, scale); s[k].w = __fmul_rn(s[k].w, scale);
+                a0 = fmaf(s[k].x, s[k].x, a0); a1 = fmaf(s[k].y, s[k].y, a1);
+                a2 = fmaf(s[k].z, s[k].z, a2); a3 = fmaf(s[k].w, s[k].w, a3);
+                mc_st4(m + 4 * i, s[k]);
               }
-              s.x = __fmul_rn(s.x, scale); s.y = __fmul_rn(s.y, scale);
-              s.z = __fmul_rn(s.z, scale); s.w = __fmul_rn(s.w, scale);
-              a0 = fmaf(s.x, s.x, a0); a1 = fmaf(s.y, s.y, a1);
-              a2 = fmaf(s.z, s.z, a2); a3 = fmaf(s.w, s.w, a3);
-#pragma unroll
-              for (int q = 0; q < W; ++q) st_peer4(g[q] + 4 * i, s);
             }
           }
-        }
-        const int i = (nvec << 2) + tid;
-        if (i < count) {
-          float s = g[0][i];
-#pragma unroll
-          for (int q = 1; q < W; ++q) s = __fadd_rn(s, g[q][i]);
-          s = __fmul_rn(s, scale);
-          a0 = fmaf(s, s, a0);
-#pragma unroll
-          for (int q = 0; q < W; ++q) g[q][i] = s;
+          const int i = (nvec << 2) + tid;
+          if (i < count) {
+            const float v = __fmul_rn(mc_ld_reduce1(m + i), scale);
+            a0 = fmaf(v, v, a0);
+            mc_st1(m + i, v);
+          }
+        } else {
+          for (int i = tid; i < count; i += COMM_THREADS) {
+            const float v = __fmul_rn(mc_ld_reduce1(m + i), scale);
+            a0 = fmaf(v, v, a0);
+            mc_st1(m + i, v);
+          }
         }
       } else {
-        for (int i = tid; i < count; i += COMM_THREADS) {
-          float s = g[0][i];
-#pragma unroll
-          for (int q = 1; q < W; ++q) s = __fadd_rn(s, g[q][i]);
-          s = __fmul_rn(s, scale);
-          a0 = fmaf(s, s, a0);
-#pragma unroll
-          for (int q = 0; q < W; ++q) g[q][i] = s;
+        float* g[W];
+  #pragma unroll
+        for (int q = 0; q < W; ++q) g[q] = reinterpret_cast<float*>(peers.arena[q] + off);
+        if ((off & 15) == 0) {
+          const int nvec = count >> 2;
+          for (int i0 = tid; i0 < nvec; i0 += COMM_THREADS * COMM_UNROLL) {
+            float4 x[COMM_UNROLL][W];
+  #pragma unroll
+            for (int k = 0; k < COMM_UNROLL; ++k) {
+              const int i = i0 + k * COMM_THREADS;
+              if (i < nvec) {
+  #pragma unroll
+                for (int q = 0; q < W; ++q) x[k][q] = ld_peer4(g[q] + 4 * i);
+              }
+            }
+  #pragma unroll
+            for (int k = 0; k < COMM_UNROLL; ++k) {
+              const int i = i0 + k * COMM_THREADS;
+              if (i < nvec) {
+                float4 s = x[k][0];
+  #pragma unroll
+                for (int q = 1; q < W; ++q) {   // fixed rank order: identical on every owner
+                  s.x = __fadd_rn(s.x, x[k][q].x);
+                  s.y = __fadd_rn(s.y, x[k][q].y);
+                  s.z = __fadd_rn(s.z, x[k][q].z);
+                  s.w = __fadd_rn(s.w, x[k][q].w);
+                }
+                s.x = __fmul_rn(s.x, scale); s.y = __fmul_rn(s.y, scale);
+                s.z = __fmul_rn(s.z, scale); s.w = __fmul_rn(s.w, scale);
+                a0 = fmaf(s.x, s.x, a0); a1 = fmaf(s.y, s.y, a1);
+                a2 = fmaf(s.z, s.z, a2); a3 = fmaf(s.w, s.w, a3);
+  #pragma unroll
+                for (int q = 0; q < W; ++q) st_peer4(g[q] + 4 * i, s);
+              }
+            }
+          }
+          const int i = (nvec << 2) + tid;
+          if (i < count) {
+            float s = g[0][i];
+  #pragma unroll
+            for (int q = 1; q < W; ++q) s = __fadd_rn(s, g[q][i]);
+            s = __fmul_rn(s, scale);
+            a0 = fmaf(s, s, a0);
+  #pragma unroll
+            for (int q = 0; q < W; ++q) g[q][i] = s;
+          }
+        } else {
+          for (int i = tid; i < count; i += COMM_THREADS) {
+            float s = g[0][i];
+  #pragma unroll
+            for (int q = 1; q < W; ++q) s = __fadd_rn(s, g[q][i]);
+            s = __fmul_rn(s, scale);
+            a0 = fmaf(s, s, a0);
+  #pragma unroll
+            for (int q = 0; q < W; ++q) g[q][i] = s;
+          }
         }
       }
       double sd = (double)a0 + (double)a1 + ((double)a2 + (double)a3);
@@ -188,12 +254,13 @@ rk_allreduce_norm_kernel(const CommPeers peers, int rank, const char* __restrict
 struct rk_comm {
   int rank, world, device, sms;
   CommPeers peers;
+  char* mc_arena;   // multicast mapping of all arenas, or nullptr
   unsigned long long scratch_off;
   unsigned long long epoch[RK_COMM_MAX_BUCKETS];
 };
 
 extern "C" int rk_comm_create(rk_comm** out, int rank, int world, void* const* arenas,
-                              uint64_t scratch_offset) {
+                              void* multicast_arena, uint64_t scratch_offset) {
   RK_REQUIRE(out && arenas, RK_ERR_INVALID, "rk_comm_create: null argument");
   RK_REQUIRE(world == 2 || world == 4 || world == 8, RK_ERR_UNSUPPORTED,
              "rk_comm_create: world size %d (supported: 2, 4, 8)", world);
@@ -205,6 +272,7 @@ extern "C" int rk_comm_create(rk_comm** out, int rank, int world, void* const* a
   c->rank = rank;
   c->world = world;
   c->scratch_off = scratch_offset;
+  c->mc_arena = (char*)multicast_arena;
   for (int q = 0; q < RK_COMM_MAX_WORLD; ++q) c->peers.arena[q] = nullptr;
   for (int q = 0; q < world; ++q) {
     if (!arenas[q]) {
@@ -227,7 +295,7 @@ extern "C" int rk_comm_create(rk_comm** out, int rank, int world, void* const* a
 
 extern "C" int rk_comm_allreduce_norm(rk_comm* c, const void* plan_host, const void* plan_dev,
                                       int chunk_lo, int chunk_hi, int bucket, int max_ctas,
-                                      void* stream) {
+                                      int use_multicast, void* stream) {
   RK_REQUIRE(c && plan_host && plan_dev, RK_ERR_INVALID, "rk_comm_allreduce_norm: null argument");
   const rk_plan_header* h = (const rk_plan_header*)plan_host;
   RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "rk_comm_allreduce_norm: bad plan magic");
@@ -244,13 +312,14 @@ extern "C" int rk_comm_allreduce_norm(rk_comm* c, const void* plan_host, const v
   const unsigned long long epoch = ++c->epoch[bucket];
   const float scale = 1.0f / (float)W;
   cudaStream_t s = (cudaStream_t)stream;
-#define RK_LAUNCH(WW)                                                                        \
-  rk_allreduce_norm_kernel<WW><<<grid, COMM_THREADS, 0, s>>>(c->peers, c->rank,              \
-      (const char*)plan_dev, c->scratch_off, chunk_lo, chunk_hi, bucket, scale, epoch)
+  const bool mc = c->mc_arena != nullptr && use_multicast != 0;
+#define RK_LAUNCH(WW, MC)                                                                    \
+  rk_allreduce_norm_kernel<WW, MC><<<grid, COMM_THREADS, 0, s>>>(c->peers, c->mc_arena,      \
+      c->rank, (const char*)plan_dev, c->scratch_off, chunk_lo, chunk_hi, bucket, scale, epoch)
   switch (W) {
-    case 2: RK_LAUNCH(2); break;
-    case 4: RK_LAUNCH(4); break;
-    case 8: RK_LAUNCH(8); break;
+    case 2: if (mc) RK_LAUNCH(2, true); else RK_LAUNCH(2, false); break;
+    case 4: if (mc) RK_LAUNCH(4, true); else RK_LAUNCH(4, false); break;
+    case 8: if (mc) RK_LAUNCH(8, true); else RK_LAUNCH(8, false); break;
   }
 #undef RK_LAUNCH
   RK_CUDA(cudaGetLastError());

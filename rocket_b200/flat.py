@@ -92,7 +92,8 @@ class EngineOptimizer:
             sig = N.RK_COMM_SIGNAL_BYTES
             scratch = -(-self.engine.backend.scratch_bytes([p.numel() for p in self._params])
                         // 256) * 256
-            self.arena = torch.zeros(sig + scratch + 4 * off, dtype=torch.uint8, device=dev)
+            from rocket_b200.comm import alloc_arena
+            self.arena = alloc_arena(sig + scratch + 4 * off, dev)
             self._scratch_offset = sig
             self._scratch_view = self.arena[sig:sig + scratch]
             self.flat_g = self.arena[sig + scratch:].view(torch.float32)

@@ -95,15 +95,17 @@ def test_fused_nvlink_allreduce_equals_nccl_path_bitwise(tmp_path):
     assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
 
 
-def _allreduce_worker(rank: int, world: int, port: int, out_dir: str) -> None:
+def _allreduce_worker(rank: int, world: int, port: int, out_dir: str, arena_kind: str,
+                      multicast: bool) -> None:
     os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
-                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
+                      ROCKET_B200_ARENA=arena_kind)
     root = Path(__file__).resolve().parent.parent
     sys.path.insert(0, str(root))
     import torch.distributed as dist
     from rocket_b200 import _native as N
     from rocket_b200.backend import NativeBackend, TensorSpec
-    from rocket_b200.comm import P2PGradSync
+    from rocket_b200.comm import alloc_arena, map_arena
     dev = torch.device("cuda", rank)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev)
@@ -115,7 +117,7 @@ def _allreduce_worker(rank: int, world: int, port: int, out_dir: str) -> None:
         total += (n + 63) // 64 * 64
     sig = N.RK_COMM_SIGNAL_BYTES
     scratch = -(-be.scratch_bytes(sizes) // 256) * 256
-    arena = torch.zeros(sig + scratch + 4 * total, dtype=torch.uint8, device=dev)
+    arena = alloc_arena(sig + scratch + 4 * total, dev)
     flat = arena[sig + scratch:].view(torch.float32)
     views = [flat[o:o + n] for o, n in zip(offs, sizes)]
     specs = [TensorSpec(p=torch.zeros(n, device=dev), g=v, m=None, v=None, group=0)
@@ -124,8 +126,13 @@ def _allreduce_worker(rank: int, world: int, port: int, out_dir: str) -> None:
 
     class Eng:
         device, process_index, num_processes = dev, rank, world
-    peers = P2PGradSync._map_peers(arena, Eng)
-    comm = be.comm_create(rank, world, [t.data_ptr() for t in peers], sig)
+    ptrs, mc_ptr, peers = map_arena(arena, Eng)
+    if multicast and not mc_ptr:
+        dist.barrier()
+        dist.destroy_process_group()
+        Path(out_dir, f"skipped_{rank}").write_text("no multicast support")
+        return
+    comm = be.comm_create(rank, world, ptrs, sig, mc_ptr)
     dist.barrier()
     stream = torch.cuda.current_stream().cuda_stream
     half = plan.n_chunks_norm // 2
@@ -139,8 +146,8 @@ def _allreduce_worker(rank: int, world: int, port: int, out_dir: str) -> None:
         want /= world
         torch.cuda.synchronize()
         dist.barrier()
-        be.comm_allreduce_norm(comm, plan, half, plan.n_chunks_norm, 0, 0, stream)   # two buckets
-        be.comm_allreduce_norm(comm, plan, 0, half, 1, 0, stream)
+        be.comm_allreduce_norm(comm, plan, half, plan.n_chunks_norm, 0, 0, stream, multicast)
+        be.comm_allreduce_norm(comm, plan, 0, half, 1, 0, stream, multicast)   # two buckets
         norm = be.l2norm_finalize(plan, want_tensor_norms=True).clone()
         torch.cuda.synchronize()
         got = flat.clone()
@@ -169,7 +176,15 @@ def _allreduce_worker(rank: int, world: int, port: int, out_dir: str) -> None:
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_fused_allreduce_norm_kernel_against_nccl(world, tmp_path):
+@pytest.mark.parametrize("path", ["ipc-p2p", "symm-p2p", "symm-multicast"])
+def test_fused_allreduce_norm_kernel_against_nccl(world, path, tmp_path):
+    """The exchange kernel on its own, with the arena shared through CUDA IPC or torch's
+    symmetric memory, using P2P loads/stores or the NVSwitch multicast (multimem) path."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    mp.spawn(_allreduce_worker, args=(world, 29870 + world, str(tmp_path)), nprocs=world, join=True)
+    kind, mode = path.split("-")
+    port = 29870 + world * 3 + ["ipc-p2p", "symm-p2p", "symm-multicast"].index(path)
+    mp.spawn(_allreduce_worker, args=(world, port, str(tmp_path), kind, mode == "multicast"),
+             nprocs=world, join=True)
+    if (tmp_path / "skipped_0").exists():
+        pytest.skip("this box has no NVSwitch multicast support")

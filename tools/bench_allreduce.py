@@ -7,7 +7,7 @@ sys.path.insert(0, str(ROOT))
 import torch, torch.distributed as dist
 from rocket_b200.backend import NativeBackend, TensorSpec
 from rocket_b200 import _native as N
-from rocket_b200.comm import P2PGradSync
+from rocket_b200.comm import alloc_arena, map_arena
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 27
 iters = 20
@@ -17,14 +17,15 @@ dist.init_process_group("nccl", device_id=dev)
 be = NativeBackend(dev)
 sig = N.RK_COMM_SIGNAL_BYTES
 scratch = -(-be.scratch_bytes([n]) // 256) * 256
-arena = torch.zeros(sig + scratch + 4 * n, dtype=torch.uint8, device=dev)
+arena = alloc_arena(sig + scratch + 4 * n, dev)
 g = arena[sig + scratch:].view(torch.float32)
 p = torch.zeros(n, device=dev)
 plan = be.make_plan([TensorSpec(p=p, g=g, m=None, v=None, group=0)], scratch=arena[sig:sig + scratch])
 class E: pass
 eng = E(); eng.device = dev; eng.process_index = rank; eng.num_processes = world
-peers = P2PGradSync._map_peers(arena, eng)
-comm = be.comm_create(rank, world, [t.data_ptr() for t in peers], sig)
+ptrs, mc_ptr, peers = map_arena(arena, eng)
+comm = be.comm_create(rank, world, ptrs, sig, mc_ptr)
+if rank == 0: print('arena', 'symm' if getattr(arena, '_rk_symm', False) else 'ipc', 'multicast_ptr', hex(mc_ptr))
 dist.barrier()
 ref = torch.empty(n, device=dev)
 def fill():
@@ -38,12 +39,13 @@ def timed(fn):
         if i >= 3: ts.append(e0.elapsed_time(e1))
     t = torch.tensor([sum(ts) / len(ts)], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t)
-for ctas in (0, 74, 296):
+for mc in ([False, True] if mc_ptr else [False]):
+  for ctas in (0, 74, 296):
     def fused():
-        be.comm_allreduce_norm(comm, plan, 0, plan.n_chunks_norm, 0, ctas, torch.cuda.current_stream().cuda_stream)
+        be.comm_allreduce_norm(comm, plan, 0, plan.n_chunks_norm, 0, ctas, torch.cuda.current_stream().cuda_stream, mc)
         be.l2norm_finalize(plan)
     t_f = timed(fused); nf = float(plan.total_norm)
-    if rank == 0: print(f"fused ctas={ctas or 148}: {t_f:.3f} ms  busbw {2*(world-1)/world*4*n/t_f/1e6:.1f} GB/s  norm {nf:.6g}")
+    if rank == 0: print(f"fused {'multimem' if mc else 'p2p'} ctas={ctas or 148}: {t_f:.3f} ms  busbw {2*(world-1)/world*4*n/t_f/1e6:.1f} GB/s  norm {nf:.6g}")
 def nccl():
     dist.all_reduce(g); be.l2norm(plan, 1.0 / world)
 t_n = timed(nccl); nn = float(plan.total_norm)

@@ -6,7 +6,7 @@ sys.path.insert(0, str(ROOT))
 import torch, torch.distributed as dist
 from rocket_b200 import _native as N
 from rocket_b200.backend import NativeBackend, TensorSpec
-from rocket_b200.comm import P2PGradSync
+from rocket_b200.comm import alloc_arena, map_arena
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 dev = torch.device("cuda", rank); torch.cuda.set_device(dev)
 dist.init_process_group("nccl", device_id=dev)
@@ -17,14 +17,14 @@ for n in sizes:
     offs.append(total); total += (n + 63) // 64 * 64
 sig = N.RK_COMM_SIGNAL_BYTES
 scratch = -(-be.scratch_bytes(sizes) // 256) * 256
-arena = torch.zeros(sig + scratch + 4 * total, dtype=torch.uint8, device=dev)
+arena = alloc_arena(sig + scratch + 4 * total, dev)
 flat = arena[sig + scratch:].view(torch.float32)
 views = [flat[o:o + n] for o, n in zip(offs, sizes)]
 specs = [TensorSpec(p=torch.zeros(n, device=dev), g=v, m=None, v=None, group=0) for n, v in zip(sizes, views)]
 plan = be.make_plan(specs, scratch=arena[sig:sig + scratch])
 class Eng: device, process_index, num_processes = dev, rank, world
-peers = P2PGradSync._map_peers(arena, Eng)
-comm = be.comm_create(rank, world, [t.data_ptr() for t in peers], sig)
+ptrs, mc_ptr, peers = map_arena(arena, Eng)
+comm = be.comm_create(rank, world, ptrs, sig, mc_ptr)
 dist.barrier()
 stream = torch.cuda.current_stream().cuda_stream
 mode = sys.argv[1] if len(sys.argv) > 1 else "two"
