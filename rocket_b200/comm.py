@@ -159,6 +159,8 @@ class P2PGradSync(_BucketedSync):
         want_mc = os.environ.get("ROCKET_B200_MULTICAST", "auto")
         self.use_multicast = bool(self.multicast_ptr) and (
             want_mc == "1" or (want_mc == "auto" and engine.num_processes >= 4))
+        if self.use_multicast and self.max_ctas == 0:
+            self.max_ctas = 74      # the switch does the work: half the SMs issue enough
         self._comm = self.backend.comm_create(
             engine.process_index, engine.num_processes, ptrs, opt._scratch_offset,
             self.multicast_ptr)
