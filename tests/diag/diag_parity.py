@@ -1,7 +1,7 @@
 """Diagnostic (GPU): how far apart are the arms after N steps of the mnist-shaped graph?"""
 import os, sys
 from pathlib import Path
-ROOT = Path(__file__).resolve().parent.parent
+ROOT = Path(__file__).resolve().parents[2]
 sys.path.insert(0, str(ROOT)); sys.path.insert(0, str(ROOT / "tests"))
 os.environ["TQDM_DISABLE"] = "1"
 import torch
