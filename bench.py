@@ -406,6 +406,8 @@ def run_ours(args) -> dict:
             "note": "bus GB/s = 2(W-1)/W x bytes / kernel time = bytes crossing NVLink per "
                     "direction per GPU; peak = measured peer-copy bandwidth (B200_PROFILING.md); "
                     "kernel time includes waiting for the slowest rank's backward"}
+    if world > 1 and not args.no_optstep and out["config"]["grad_sync"] == "P2PGradSync":
+        out["optstep"] = optstep_microbench_dp(peak, rank, world, local)
     if rank == 0 and world == 1 and not args.no_optstep:
         out["optstep"] = optstep_microbench(peak)
     if rank == 0 and world == 1 and not args.no_cpu and args.workload == "resnet18":
@@ -450,6 +452,71 @@ def optstep_microbench(peak: float, n: int = 1_000_000_000, steps: int = 20, war
             "full_step_gbs_36B": round(gbs_full, 1),
             "frac_of_measured_peak": round(gbs_full / peak, 4),
             "frac_of_nominal_8000": round(gbs_full / 8000.0, 4)}
+
+
+def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
+                          n: int = 1_000_000_000, steps: int = 10, warmup: int = 3):
+    """configs[4] at N > 1: every rank holds a full replica of 1e9 fp32 params; per step the
+    gradients (different per rank) are averaged by the fused NVLink exchange kernel, which
+    also yields the norm partials, then finalize + fused AdamW + clip + zero_grad.  Timed on
+    the device with CUDA events, max over ranks."""
+    from rocket_b200 import _native as N
+    from rocket_b200.backend import NativeBackend, TensorSpec
+    from rocket_b200.comm import alloc_arena, map_arena
+    dev = torch.device("cuda", local)
+    be = NativeBackend(dev)
+    sig = N.RK_COMM_SIGNAL_BYTES
+    scratch = -(-be.scratch_bytes([n]) // 256) * 256
+    arena = alloc_arena(sig + scratch + 4 * n, dev)
+    g = arena[sig + scratch:].view(torch.float32)
+    p = torch.randn(n, device=dev) * 0.02
+    m = torch.zeros(n, device=dev)
+    v = torch.zeros(n, device=dev)
+    plan = be.make_plan([TensorSpec(p=p, g=g, m=m, v=v, group=0)], scratch=arena[sig:sig + scratch])
+
+    class Eng:
+        device, process_index, num_processes = dev, rank, world
+    ptrs, mc_ptr, keep = map_arena(arena, Eng)
+    comm = be.comm_create(rank, world, ptrs, sig, mc_ptr)
+    dist.barrier()
+    use_mc = bool(mc_ptr) and world >= 4
+    hp = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2, decoupled=True)
+    stream = torch.cuda.current_stream().cuda_stream
+    tx, ts = [], []
+    for i in range(warmup + steps):
+        torch.manual_seed(1000 * i + rank)
+        g.normal_(0, 1e-3)
+        torch.cuda.synchronize()
+        dist.barrier()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
+        be.comm_allreduce_norm(comm, plan, 0, plan.n_chunks_norm, 0, 74 if use_mc else 0, stream,
+                               use_mc)
+        norm = be.l2norm_finalize(plan)
+        e[1].record()
+        be.adam_step(plan, [dict(hp, step=i + 1)], norm, 1.0, 1.0, True)
+        e[2].record()
+        torch.cuda.synchronize()
+        if i >= warmup:
+            tx.append(e[0].elapsed_time(e[1]))
+            ts.append(e[1].elapsed_time(e[2]))
+    t = torch.tensor([statistics.mean(tx), statistics.mean(ts)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    t_x, t_s = float(t[0]), float(t[1])
+    dist.barrier()
+    be.comm_destroy(comm)
+    del keep, p, m, v, g, plan, arena
+    torch.cuda.ipc_collect()
+    torch.cuda.empty_cache()
+    bus = 2 * (world - 1) / world * 4 * n / (t_x * 1e-3) / 1e9
+    return {"params": n, "layout": "one flat fp32 tensor, full replica per rank", "steps": steps,
+            "exchange": "NVSwitch multimem" if use_mc else "NVLink P2P",
+            "exchange_plus_norm_ms": round(t_x, 4), "exchange_bus_gbs": round(bus, 1),
+            "step_kernel_ms": round(t_s, 4),
+            "step_kernel_gbs": round(ALGO_BYTES_STEP * n / (t_s * 1e-3) / 1e9, 1),
+            "ms_per_optimizer_step": round(t_x + t_s, 4),
+            "step_kernel_frac_of_measured_peak":
+                round(ALGO_BYTES_STEP * n / (t_s * 1e-3) / 1e9 / peak, 4)}
 
 
 def cpu_port(budget_s: float, threads, as_line: bool, steps=None, warmup=1):
