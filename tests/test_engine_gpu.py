@@ -177,3 +177,34 @@ def test_deferred_loss_does_not_sync_per_step():
     finally:
         rk.Launcher.engine_factory = old
     assert sum(short.values()) == sum(long.values()), (short, long)
+
+
+def test_checkpoint_resume_is_bit_exact_and_torch_compatible(tmp_path):
+    """save mid-run, resume, land on the same bits as an uninterrupted
+    run; the optimizer file is an ordinary torch state_dict (flat moments exported per tensor)."""
+    import rocket_b200 as rk
+    kw = dict(optimizer="adamw", n_train=64 * 6, accum=1, max_norm=0.5, clip_via="kwarg")
+
+    def run(epochs, tag=None, save=False):
+        launcher, h = workloads.build_mnist_graph(rk, **dict(kw, epochs=epochs))
+        if tag:
+            launcher._tag, launcher._logging_dir = tag, str(tmp_path)
+        if save:
+            launcher._capsules[0]._capsules.append(rk.Checkpointer(save_every=6))
+        return launcher, h
+
+    launcher, h1 = run(1, tag="a", save=True)
+    launcher.launch()
+    ckpt = tmp_path / "a" / "v0" / "weights" / "005"
+    sd = torch.load(ckpt / "optimizer_0.pt", map_location="cpu")
+    assert set(sd["state"][0]) >= {"step", "exp_avg", "exp_avg_sq"} and float(sd["state"][0]["step"]) == 6
+    plain = torch.optim.AdamW(workloads.LeNet().parameters())
+    plain.load_state_dict(sd)                                   # loads into stock torch
+
+    launcher, h2 = run(2)
+    launcher.launch()                                           # 12 steps straight
+    launcher, h3 = run(2)
+    launcher._epoch_idx = 1
+    launcher.resume(str(ckpt), load_capsules=False).launch()   # 6 restored + 6 new
+    for (k, a), (_, b) in zip(h2["net"].named_parameters(), h3["net"].named_parameters()):
+        assert torch.equal(a, b), k
