@@ -184,6 +184,22 @@ int rk_sgd_step_multi(const void* plan_host, const void* plan_dev,
                       const float* total_norm_dev, float max_norm,
                       float grad_scale, int zero_grads, void* stream);
 
+/* ---- K2/K3 with the per-group constants in device memory ---------------------------------
+ * For CUDA-graph replays, where kernel arguments are frozen at capture: rk_*_table_write
+ * derives the same per-group constants as the calls above into RK_STEP_TABLE_BYTES of
+ * caller memory (host side; typically a pinned slot), the caller copies them to
+ * `table_dev` in stream order, and the *_devtable launches read them from there.  Same
+ * kernels, same arithmetic.                                                              */
+#define RK_STEP_TABLE_BYTES 4096
+int rk_adam_table_write(const rk_adam_group* groups, int n_groups, void* table_out);
+int rk_sgd_table_write(const rk_sgd_group* groups, int n_groups, void* table_out);
+int rk_adamw_step_multi_devtable(const void* plan_host, const void* plan_dev,
+                                 const void* table_dev, const float* total_norm_dev,
+                                 float max_norm, float grad_scale, int zero_grads, void* stream);
+int rk_sgd_step_multi_devtable(const void* plan_host, const void* plan_dev,
+                               const void* table_dev, const float* total_norm_dev,
+                               float max_norm, float grad_scale, int zero_grads, void* stream);
+
 /* ---- K4: Meter reductions on the device -----------------------------------------
  * counters[0] += #rows whose argmax(logits[row, :]) == labels[row];
  * counters[1] += n_rows.   Integer atomics: bit-exact and order independent.

@@ -17,6 +17,7 @@ LIB_PATH = Path(__file__).resolve().parent / "csrc" / "librocket_b200.so"
 RK_MAX_GROUPS = 64
 RK_TENSOR_SKIP = 1
 RK_COMM_SIGNAL_BYTES = 36864
+RK_STEP_TABLE_BYTES = 4096
 RK_COMM_MAX_BUCKETS = 256
 EXPORTS = [
     "rk_version", "rk_last_error", "rk_launch_count", "rk_plan_query", "rk_plan_build",
@@ -24,7 +25,8 @@ EXPORTS = [
     "rk_sgd_step_multi",
     "rk_meter_argmax_count", "rk_scalar_accumulate", "rk_stage_create", "rk_stage_submit",
     "rk_stage_wait", "rk_stage_release", "rk_stage_destroy", "rk_l2norm_finalize",
-    "rk_comm_create", "rk_comm_allreduce_norm", "rk_comm_destroy",
+    "rk_comm_create", "rk_comm_allreduce_norm", "rk_comm_destroy", "rk_adam_table_write",
+    "rk_sgd_table_write", "rk_adamw_step_multi_devtable", "rk_sgd_step_multi_devtable",
 ]
 
 
@@ -91,6 +93,12 @@ def load() -> ctypes.CDLL:
     lib.rk_comm_allreduce_norm.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                            c_int, c_int, c_void_p]
     lib.rk_comm_destroy.argtypes = [c_void_p]
+    lib.rk_adam_table_write.argtypes = [POINTER(AdamGroup), c_int, c_void_p]
+    lib.rk_sgd_table_write.argtypes = [POINTER(SgdGroup), c_int, c_void_p]
+    lib.rk_adamw_step_multi_devtable.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                                 c_float, c_int, c_void_p]
+    lib.rk_sgd_step_multi_devtable.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                               c_float, c_int, c_void_p]
     for name in EXPORTS:
         fn = getattr(lib, name)          # AttributeError here = header/library mismatch
         if name not in ("rk_last_error", "rk_launch_count"):

@@ -137,13 +137,45 @@ class NativeBackend:
         return plan.total_norm
 
     # K2
-    def adam_step(self, plan: Plan, groups: list[dict], total_norm, max_norm: float,
-                  grad_scale: float, zero_grads: bool) -> None:
+    @staticmethod
+    def _adam_groups(groups: list[dict]):
         arr = (N.AdamGroup * len(groups))()
         for a, g in zip(arr, groups):
             a.lr, a.beta1, a.beta2 = g["lr"], g["beta1"], g["beta2"]
             a.eps, a.weight_decay, a.step = g["eps"], g["weight_decay"], g["step"]
             a.decoupled, a.skip = int(g["decoupled"]), int(g.get("skip", False))
+        return arr
+
+    @staticmethod
+    def _sgd_groups(groups: list[dict]):
+        arr = (N.SgdGroup * len(groups))()
+        for a, g in zip(arr, groups):
+            a.lr, a.momentum, a.dampening = g["lr"], g["momentum"], g["dampening"]
+            a.weight_decay, a.nesterov = g["weight_decay"], int(g["nesterov"])
+            a.first_step, a.skip = int(g["first_step"]), int(g.get("skip", False))
+        return arr
+
+    def step_table_write(self, kind: str, groups: list[dict], out: torch.Tensor) -> None:
+        """Per-group constants of one step into RK_STEP_TABLE_BYTES of host memory (graph
+        replays: the table is then copied to the device in stream order)."""
+        if kind == "sgd":
+            N.check(self.lib.rk_sgd_table_write(self._sgd_groups(groups), len(groups),
+                                                out.data_ptr()), "rk_sgd_table_write")
+        else:
+            N.check(self.lib.rk_adam_table_write(self._adam_groups(groups), len(groups),
+                                                 out.data_ptr()), "rk_adam_table_write")
+
+    def step_devtable(self, kind: str, plan: Plan, table_dev: torch.Tensor, total_norm,
+                      max_norm: float, grad_scale: float, zero_grads: bool) -> None:
+        fn = self.lib.rk_sgd_step_multi_devtable if kind == "sgd" \
+            else self.lib.rk_adamw_step_multi_devtable
+        N.check(fn(plan.host.data_ptr(), plan.dev.data_ptr(), table_dev.data_ptr(),
+                   total_norm.data_ptr() if total_norm is not None else None, max_norm,
+                   grad_scale, int(zero_grads), self._stream()), "rk_*_step_multi_devtable")
+
+    def adam_step(self, plan: Plan, groups: list[dict], total_norm, max_norm: float,
+                  grad_scale: float, zero_grads: bool) -> None:
+        arr = self._adam_groups(groups)
         N.check(self.lib.rk_adamw_step_multi(
             plan.host.data_ptr(), plan.dev.data_ptr(), arr, len(groups),
             total_norm.data_ptr() if total_norm is not None else None, max_norm, grad_scale,
@@ -152,11 +184,7 @@ class NativeBackend:
     # K3
     def sgd_step(self, plan: Plan, groups: list[dict], total_norm, max_norm: float,
                  grad_scale: float, zero_grads: bool) -> None:
-        arr = (N.SgdGroup * len(groups))()
-        for a, g in zip(arr, groups):
-            a.lr, a.momentum, a.dampening = g["lr"], g["momentum"], g["dampening"]
-            a.weight_decay, a.nesterov = g["weight_decay"], int(g["nesterov"])
-            a.first_step, a.skip = int(g["first_step"]), int(g.get("skip", False))
+        arr = self._sgd_groups(groups)
         N.check(self.lib.rk_sgd_step_multi(
             plan.host.data_ptr(), plan.dev.data_ptr(), arr, len(groups),
             total_norm.data_ptr() if total_norm is not None else None, max_norm, grad_scale,

@@ -31,7 +31,10 @@ class Loss(Capsule):
         if not torch.is_grad_enabled():
             return
         engine = self._accelerator
-        loss = self._objective(attrs.batch)
+        gp = engine.graph_pass
+        # replaying a captured step (Module(graph=True)): objective, accumulation and backward
+        # are nodes of the graph; only the host-side bookkeeping below runs again
+        loss = None if gp is not None and gp.mode == "replay" else self._objective(attrs.batch)
         if self._acc is None:
             self._acc = engine.scalar_accumulator(initial=self._value)
         # value += mean_over_ranks(loss) / accumulation_steps      (reference loss.py:95-98)

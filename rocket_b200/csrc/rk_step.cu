@@ -149,8 +149,8 @@ __device__ __forceinline__ void stg1(float* p, float v) {
 template <class Op, class Table, int U, int MINB, int HINT>
 __global__ void __launch_bounds__(STEP_THREADS, MINB)
 rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table table,
-               const float* __restrict__ total_norm, float max_norm, float grad_scale,
-               int zero_grads) {
+               const Table* __restrict__ dtable, const float* __restrict__ total_norm,
+               float max_norm, float grad_scale, int zero_grads) {
   __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
   const int n_tensors = h->n_tensors;
@@ -171,7 +171,9 @@ rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table tabl
     const int t = rk_find_tensor(prefix, n_tensors, c);
     const rk_tensor_desc d = descs[t];
     Op op;
-    op.h = table.g[d.group];
+    // per-group constants: launch arguments, or (CUDA-graph replays, where arguments are
+    // frozen) a table in device memory that the host refreshes before each replay
+    op.h = dtable ? dtable->g[d.group] : table.g[d.group];
     if ((d.flags & RK_TENSOR_SKIP) || (op.h.flags & GROUP_SKIP)) continue;
     const int64_t base = (int64_t)(c - prefix[t]) * chunk;
     const int64_t rem = d.numel - base;
@@ -242,14 +244,14 @@ static inline bool need_m(const SgdDev& g) { return (g.flags & SGD_HAS_MOM) != 0
 
 template <class Op, class Table, int U, int MINB, int HINT>
 static int launch_variant(const rk_plan_header* h, const void* plan_dev, const Table& table,
-                          const float* total_norm_dev, float max_norm, float grad_scale,
-                          int zero_grads, void* stream) {
+                          const Table* dtable, const float* total_norm_dev, float max_norm,
+                          float grad_scale, int zero_grads, void* stream) {
   auto kernel = rk_step_kernel<Op, Table, U, MINB, HINT>;
   int grid = 0;
   int rc = rk_persistent_grid((const void*)kernel, STEP_THREADS, 0, h->n_chunks_step, &grid);
   if (rc) return rc;
   kernel<<<grid, STEP_THREADS, 0, (cudaStream_t)stream>>>(
-      (const char*)plan_dev, table, total_norm_dev, max_norm, grad_scale, zero_grads);
+      (const char*)plan_dev, table, dtable, total_norm_dev, max_norm, grad_scale, zero_grads);
   return 0;
 }
 
@@ -277,12 +279,13 @@ static int step_variant(const rk_plan_header* h) {
 template <class Op, class Table>
 static int launch_step(const void* plan_host, const void* plan_dev, const Table& table,
                        const float* total_norm_dev, float max_norm, float grad_scale,
-                       int zero_grads, void* stream, const char* who) {
+                       int zero_grads, void* stream, const char* who,
+                       const Table* dtable = nullptr) {
   RK_REQUIRE(plan_host && plan_dev, RK_ERR_INVALID, "%s: null plan", who);
   const rk_plan_header* h = (const rk_plan_header*)plan_host;
   RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "%s: bad plan magic", who);
   if (h->n_chunks_step == 0) return 0;
-  {  // state pointers the chosen optimizer needs must be present
+  if (dtable == nullptr) {  // state pointers the chosen optimizer needs must be present
     const rk_tensor_desc* d = (const rk_tensor_desc*)((const char*)plan_host + h->off_descs);
     for (int i = 0; i < h->n_tensors; ++i) {
       if ((d[i].flags & RK_TENSOR_SKIP) || d[i].numel == 0) continue;
@@ -296,7 +299,7 @@ static int launch_step(const void* plan_host, const void* plan_dev, const Table&
   }
   int rc;
 #define RK_V(U, MINB, HINT)                                                              \
-  rc = launch_variant<Op, Table, U, MINB, HINT>(h, plan_dev, table, total_norm_dev,      \
+  rc = launch_variant<Op, Table, U, MINB, HINT>(h, plan_dev, table, dtable, total_norm_dev, \
                                                 max_norm, grad_scale, zero_grads, stream)
   switch (step_variant(h)) {   // (U, resident CTAs/SM, cache hint) -- see profiles/r1_step_kernel_notes.md
     default:
@@ -344,14 +347,13 @@ extern "C" int rk_adam_derive(const rk_adam_group* g, float* out9, int* flags_ou
   return 0;
 }
 
-extern "C" int rk_adamw_step_multi(const void* plan_host, const void* plan_dev,
-                                   const rk_adam_group* groups, int n_groups,
-                                   const float* total_norm_dev, float max_norm,
-                                   float grad_scale, int zero_grads, void* stream) {
-  RK_REQUIRE(groups, RK_ERR_INVALID, "rk_adamw_step_multi: null groups");
+static_assert(sizeof(AdamTable) <= RK_STEP_TABLE_BYTES && sizeof(SgdTable) <= RK_STEP_TABLE_BYTES,
+              "RK_STEP_TABLE_BYTES too small");
+
+static int build_adam_table(const rk_adam_group* groups, int n_groups, AdamTable& tab) {
+  RK_REQUIRE(groups, RK_ERR_INVALID, "adam groups: null");
   RK_REQUIRE(n_groups > 0 && n_groups <= RK_MAX_GROUPS, RK_ERR_TOO_LARGE,
-             "rk_adamw_step_multi: n_groups=%d outside [1,%d]", n_groups, RK_MAX_GROUPS);
-  AdamTable tab;
+             "adam groups: n_groups=%d outside [1,%d]", n_groups, RK_MAX_GROUPS);
   memset(&tab, 0, sizeof(tab));
   for (int i = 0; i < RK_MAX_GROUPS; ++i) tab.g[i].flags = GROUP_SKIP;
   for (int i = 0; i < n_groups; ++i) {
@@ -363,19 +365,48 @@ extern "C" int rk_adamw_step_multi(const void* plan_host, const void* plan_dev,
     d.decay = c[0]; d.wd = c[1]; d.w1 = c[2]; d.w1m1 = c[3]; d.beta2 = c[4];
     d.w2 = c[5]; d.s2 = c[6]; d.eps = c[7]; d.neg_step = c[8]; d.flags = f;
   }
+  return 0;
+}
+
+extern "C" int rk_adamw_step_multi(const void* plan_host, const void* plan_dev,
+                                   const rk_adam_group* groups, int n_groups,
+                                   const float* total_norm_dev, float max_norm,
+                                   float grad_scale, int zero_grads, void* stream) {
+  AdamTable tab;
+  int rc = build_adam_table(groups, n_groups, tab);
+  if (rc) return rc;
   return launch_step<AdamOp, AdamTable>(plan_host, plan_dev, tab, total_norm_dev, max_norm,
                                         grad_scale, zero_grads, stream,
                                         "rk_adamw_step_multi");
 }
 
-extern "C" int rk_sgd_step_multi(const void* plan_host, const void* plan_dev,
-                                 const rk_sgd_group* groups, int n_groups,
-                                 const float* total_norm_dev, float max_norm,
-                                 float grad_scale, int zero_grads, void* stream) {
-  RK_REQUIRE(groups, RK_ERR_INVALID, "rk_sgd_step_multi: null groups");
+extern "C" int rk_adam_table_write(const rk_adam_group* groups, int n_groups, void* table_out) {
+  RK_REQUIRE(table_out, RK_ERR_INVALID, "rk_adam_table_write: null output");
+  AdamTable tab;
+  int rc = build_adam_table(groups, n_groups, tab);
+  if (rc) return rc;
+  memset(table_out, 0, RK_STEP_TABLE_BYTES);
+  memcpy(table_out, &tab, sizeof(tab));
+  return 0;
+}
+
+extern "C" int rk_adamw_step_multi_devtable(const void* plan_host, const void* plan_dev,
+                                            const void* table_dev, const float* total_norm_dev,
+                                            float max_norm, float grad_scale, int zero_grads,
+                                            void* stream) {
+  RK_REQUIRE(table_dev, RK_ERR_INVALID, "rk_adamw_step_multi_devtable: null table");
+  AdamTable unused;
+  memset(&unused, 0, sizeof(unused));
+  return launch_step<AdamOp, AdamTable>(plan_host, plan_dev, unused, total_norm_dev, max_norm,
+                                        grad_scale, zero_grads, stream,
+                                        "rk_adamw_step_multi_devtable",
+                                        (const AdamTable*)table_dev);
+}
+
+static int build_sgd_table(const rk_sgd_group* groups, int n_groups, SgdTable& tab) {
+  RK_REQUIRE(groups, RK_ERR_INVALID, "sgd groups: null");
   RK_REQUIRE(n_groups > 0 && n_groups <= RK_MAX_GROUPS, RK_ERR_TOO_LARGE,
-             "rk_sgd_step_multi: n_groups=%d outside [1,%d]", n_groups, RK_MAX_GROUPS);
-  SgdTable tab;
+             "sgd groups: n_groups=%d outside [1,%d]", n_groups, RK_MAX_GROUPS);
   memset(&tab, 0, sizeof(tab));
   for (int i = 0; i < RK_MAX_GROUPS; ++i) tab.g[i].flags = GROUP_SKIP;
   for (int i = 0; i < n_groups; ++i) {
@@ -395,6 +426,38 @@ extern "C" int rk_sgd_step_multi(const void* plan_host, const void* plan_dev,
     if (g.skip) f |= GROUP_SKIP;
     d.flags = f;
   }
+  return 0;
+}
+
+extern "C" int rk_sgd_step_multi(const void* plan_host, const void* plan_dev,
+                                 const rk_sgd_group* groups, int n_groups,
+                                 const float* total_norm_dev, float max_norm,
+                                 float grad_scale, int zero_grads, void* stream) {
+  SgdTable tab;
+  int rc = build_sgd_table(groups, n_groups, tab);
+  if (rc) return rc;
   return launch_step<SgdOp, SgdTable>(plan_host, plan_dev, tab, total_norm_dev, max_norm,
                                       grad_scale, zero_grads, stream, "rk_sgd_step_multi");
+}
+
+extern "C" int rk_sgd_table_write(const rk_sgd_group* groups, int n_groups, void* table_out) {
+  RK_REQUIRE(table_out, RK_ERR_INVALID, "rk_sgd_table_write: null output");
+  SgdTable tab;
+  int rc = build_sgd_table(groups, n_groups, tab);
+  if (rc) return rc;
+  memset(table_out, 0, RK_STEP_TABLE_BYTES);
+  memcpy(table_out, &tab, sizeof(tab));
+  return 0;
+}
+
+extern "C" int rk_sgd_step_multi_devtable(const void* plan_host, const void* plan_dev,
+                                          const void* table_dev, const float* total_norm_dev,
+                                          float max_norm, float grad_scale, int zero_grads,
+                                          void* stream) {
+  RK_REQUIRE(table_dev, RK_ERR_INVALID, "rk_sgd_step_multi_devtable: null table");
+  SgdTable unused;
+  memset(&unused, 0, sizeof(unused));
+  return launch_step<SgdOp, SgdTable>(plan_host, plan_dev, unused, total_norm_dev, max_norm,
+                                      grad_scale, zero_grads, stream,
+                                      "rk_sgd_step_multi_devtable", (const SgdTable*)table_dev);
 }

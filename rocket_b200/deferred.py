@@ -13,20 +13,30 @@ from typing import Callable
 
 
 class DeferredScalar:
-    __slots__ = ("_slot", "_event", "_finalize", "_value")
+    __slots__ = ("_slot", "_event", "_finalize", "_value", "_armed")
 
-    def __init__(self, slot, event=None, finalize: Callable | None = None):
+    def __init__(self, slot, event=None, finalize: Callable | None = None, armed: bool = True):
         self._slot = slot            # 1-element pinned host tensor (or any 0/1-elem tensor)
         self._event = event          # torch.cuda.Event or None (value already valid)
         self._finalize = finalize    # host-side post-processing of the raw number
         self._value = None
+        self._armed = armed          # False: the copy has not even been enqueued yet
+
+    def arm(self) -> None:
+        """The copy into the slot has been enqueued: record the event that guards it."""
+        self._event.record()
+        self._armed = True
 
     # ---- readiness ------------------------------------------------------------------
     def ready(self) -> bool:
-        return self._value is not None or self._event is None or self._event.query()
+        if self._value is not None:
+            return True
+        return self._armed and (self._event is None or self._event.query())
 
     def _resolve(self):
         if self._value is None:
+            if not self._armed:
+                raise RuntimeError("DeferredScalar read before its producer was enqueued")
             if self._event is not None and not self._event.query():
                 self._event.synchronize()
             raw = self._slot.item() if self._slot.numel() == 1 else self._slot.tolist()

@@ -71,6 +71,21 @@ class EngineScheduler:
         self.scheduler.load_state_dict(state)
 
 
+class GraphPass:
+    """One pass of a ``Module(graph=True)`` capsule over its children while a CUDA graph of
+    the step is being captured (``mode == "capture"``: device work is recorded, host logic
+    runs) or is about to be replayed (``mode == "replay"``: host logic only, device work is
+    already in the graph).  ``pre`` actions run on the stream right before the replay (uploads
+    of this step's scalars), ``post`` actions right after it (read-backs).  ``slots`` keeps the
+    graph's static tensors that participants need again on later replays."""
+
+    def __init__(self, mode: str, slots: dict):
+        self.mode = mode
+        self.slots = slots
+        self.pre: list = []
+        self.post: list = []
+
+
 class ScalarAccumulator:
     """Device-side running sum for the Loss capsule (reference rocket/core/loss.py:95-116)."""
 
@@ -82,7 +97,10 @@ class ScalarAccumulator:
         self._ring = None
         self._ring_pos = 0
 
-    def add(self, value: torch.Tensor, divisor: float) -> None:
+    def add(self, value, divisor: float) -> None:
+        gp = self.engine.graph_pass
+        if gp is not None and gp.mode == "replay":
+            return                                   # the accumulate kernel is in the graph
         self.engine.backend.scalar_accumulate(value.detach(), divisor, self.acc)
 
     def _slot(self) -> torch.Tensor:
@@ -96,6 +114,9 @@ class ScalarAccumulator:
 
     def publish_and_reset(self) -> DeferredScalar:
         eng = self.engine
+        gp = eng.graph_pass
+        if gp is not None:
+            return self._publish_in_graph(gp)
         out = self.acc.clone()
         self.acc.zero_()
         if eng.num_processes > 1:                 # mean over ranks, as gather(loss).mean()
@@ -108,6 +129,27 @@ class ScalarAccumulator:
             event = torch.cuda.Event()
             event.record()
         return DeferredScalar(slot, event)
+
+    def _publish_in_graph(self, gp: GraphPass) -> DeferredScalar:
+        """Graph passes: snapshot + reset are nodes of the graph writing a static tensor; the
+        copy to the pinned ring happens after each replay."""
+        eng = self.engine
+        if gp.mode == "capture":
+            out = self.acc.clone()
+            self.acc.zero_()
+            if eng.num_processes > 1:
+                dist.all_reduce(out, op=dist.ReduceOp.SUM)
+                out /= eng.num_processes
+            gp.slots[("loss", id(self))] = out
+        out = gp.slots[("loss", id(self))]
+        slot = self._slot()
+        value = DeferredScalar(slot, torch.cuda.Event(), armed=False)
+
+        def read_back():
+            slot.copy_(out, non_blocking=True)
+            value.arm()
+        gp.post.append(read_back)
+        return value
 
     def peek(self) -> float:
         return float(self.acc.item())
@@ -168,6 +210,7 @@ class Engine:
         self._buffer_sync: list = []
         self._bucket_cap_mb = bucket_cap_mb
         self._p2p = None
+        self.graph_pass: GraphPass | None = None    # set by Module(graph=True) around a pass
         self.grad_sync_kinds: list[str] = []      # which exchange each optimizer got
         self.stager = None
         if self.device.type == "cuda" and stage_batches:
@@ -276,6 +319,8 @@ class Engine:
     def backward(self, loss: torch.Tensor, **kwargs) -> None:
         """reference loss.py:119: scale by 1/accumulation_steps, then autograd.  Bucketed
         all-reduces start from gradient hooks while this runs (sync steps only)."""
+        if self.graph_pass is not None and self.graph_pass.mode == "replay":
+            return                                   # backward is part of the graph
         (loss / self._accum_steps).backward(**kwargs)
 
     # ---- gradient exchange -----------------------------------------------------------------------------

@@ -121,7 +121,8 @@ class EngineOptimizer:
         self._group_step = [0] * len(self.optimizer.param_groups)
         self._import_state()
         self._plan = None
-        self._plan_skip = None
+        self._table_ring = None
+        self._dev_table = torch.zeros(4096, dtype=torch.uint8, device=dev)
 
     def _import_state(self) -> None:
         """Adopt state the wrapped optimizer already holds (resume / prior training)."""
@@ -173,6 +174,10 @@ class EngineOptimizer:
     def clip_grad_norm_(self, max_norm: float) -> torch.Tensor:
         """Engine-level ``clip_grad_norm_``: computes the global norm now (one kernel) and
         applies the coefficient inside the next fused step.  Returns the device norm."""
+        gp = self.engine.graph_pass
+        if gp is not None and gp.mode == "replay":     # the norm kernel is part of the graph
+            self._pending_clip = float(max_norm)
+            return self.last_grad_norm
         self._adopt_grads()
         plan = self._get_plan()
         if self.engine.finish_grad_sync(self):
@@ -189,21 +194,48 @@ class EngineOptimizer:
         eng = self.engine
         if not eng.sync_gradients:
             return
-        self._adopt_grads()
-        plan = self._get_plan()
-        fused_norm = eng.finish_grad_sync(self)      # True: norm partials are in plan.scratch
-        scale = eng.grad_scale(self)
+        gp = eng.graph_pass                      # None, or a Module's CUDA-graph pass
+        replay = gp is not None and gp.mode == "replay"
         max_norm = self._pending_clip if self._pending_clip is not None else self.max_grad_norm
-        norm = None
-        if max_norm is not None:
-            if self._pending_clip is not None:
-                norm = self.last_grad_norm
-            elif fused_norm:
-                norm = eng.backend.l2norm_finalize(plan)
-            else:
-                norm = eng.backend.l2norm(plan, scale)
-            self.last_grad_norm = norm
+        if not replay:
+            self._adopt_grads()
+            if gp is not None and self._plan is None:
+                raise RuntimeError("CUDA-graph capture before the optimizer's first eager step")
+            plan = self._get_plan()
+            fused_norm = eng.finish_grad_sync(self)  # True: norm partials are in plan.scratch
+            scale = eng.grad_scale(self)
+            norm = None
+            if max_norm is not None:
+                if self._pending_clip is not None:
+                    norm = self.last_grad_norm
+                elif fused_norm:
+                    norm = eng.backend.l2norm_finalize(plan)
+                else:
+                    norm = eng.backend.l2norm(plan, scale)
+                self.last_grad_norm = norm
         self._pending_clip = None
+        groups = self._step_groups()
+        if gp is None:
+            fn = eng.backend.sgd_step if self._kind == "sgd" else eng.backend.adam_step
+            fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)
+        else:
+            # Kernel arguments are frozen inside a graph: this step's constants go through a
+            # pinned ring slot into a device table, uploaded in stream order before the replay.
+            slot = self._table_slot()
+            eng.backend.step_table_write(self._kind, groups, slot)
+            table = self._dev_table
+            gp.pre.append(lambda: table.copy_(slot, non_blocking=True))
+            if not replay:
+                eng.backend.step_devtable(self._kind, plan, table, norm,
+                                          float(max_norm) if max_norm is not None else 0.0,
+                                          scale, True)
+        eng.grad_sync_step_done(self)
+        self._zeroed_by_step = True
+        self._state_dirty = True
+        self.optimizer._opt_called = True   # what torch's LRScheduler checks before warning
+
+    def _step_groups(self) -> list[dict]:
+        """This step's hyper-parameters per param group (advances the step counters)."""
         active = set(self._group_of[i] for i in range(len(self._params)) if self._adopted[i])
         groups = []
         for gi, g in enumerate(self.optimizer.param_groups):
@@ -224,12 +256,28 @@ class EngineOptimizer:
                                    decoupled=self._kind == "adamw"
                                    or bool(g.get("decoupled_weight_decay", False)),
                                    skip=skip))
-        fn = eng.backend.sgd_step if self._kind == "sgd" else eng.backend.adam_step
-        fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)
-        eng.grad_sync_step_done(self)
-        self._zeroed_by_step = True
-        self._state_dirty = True
-        self.optimizer._opt_called = True   # what torch's LRScheduler checks before warning
+        return groups
+
+    _TABLE_SLOTS = 32
+
+    def _table_slot(self) -> torch.Tensor:
+        """Next slot of the pinned ring the step tables are staged in.  A slot is reused only
+        after the upload that read it has executed, which also bounds how far the host can
+        run ahead of the device."""
+        from rocket_b200 import _native as N
+        if self._table_ring is None:
+            self._table_ring = torch.zeros(self._TABLE_SLOTS, N.RK_STEP_TABLE_BYTES,
+                                           dtype=torch.uint8).pin_memory()
+            self._table_events = [None] * self._TABLE_SLOTS
+            self._table_pos = 0
+        i = self._table_pos
+        self._table_pos = (i + 1) % self._TABLE_SLOTS
+        if self._table_events[i] is not None:
+            self._table_events[i].synchronize()
+        ev = torch.cuda.Event()
+        self._table_events[i] = ev
+        self.engine.graph_pass.post.append(ev.record)
+        return self._table_ring[i]
 
     # ---- gradient adoption -----------------------------------------------------------------------
     def _adopt_grads(self) -> None:

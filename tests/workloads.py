@@ -100,7 +100,7 @@ def make_user_clip(rk):
 def build_mnist_graph(rk, *, seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_size=64,
                       optimizer="adamw", max_norm=None, accum=2, epochs=2, sched_step=5,
                       tracker_backend=None, accuracy_cls=None, clip_via="capsule",
-                      lr=1e-3, net=None, opt_kwargs=None):
+                      lr=1e-3, net=None, opt_kwargs=None, graph=False):
     """Returns (launcher, handles) -- handles: net, opt, sched, accuracy, tracker_backend."""
     torch.manual_seed(seed)
     net = net if net is not None else LeNet()
@@ -127,8 +127,9 @@ def build_mnist_graph(rk, *, seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_s
     else:
         inner.append(rk.Optimizer(opt))
     inner.append(rk.Scheduler(sched))
+    module_kw = dict(graph=True) if graph else {}          # additive keyword of rocket_b200
     train_caps = [rk.Dataset(train, batch_size=batch_size, shuffle=False),
-                  rk.Module(net, capsules=inner)]
+                  rk.Module(net, capsules=inner, **module_kw)]
     val_caps = [rk.Dataset(val, batch_size=batch_size, shuffle=False),
                 rk.Module(net, capsules=[]),
                 rk.Meter([accuracy], keys=[1, 2])]
