@@ -197,13 +197,38 @@ def run_ours(args) -> dict:
     torch.backends.cudnn.benchmark = True
 
     class TimedBackend(NativeBackend):
-        """Brackets each engine kernel launch with CUDA events on its own stream."""
+        """Brackets each engine kernel launch with CUDA events on its own stream.  While a
+        step is being captured into a CUDA graph the events are `external` ones, i.e. event
+        record nodes of the graph: every replay re-records them and the host samples the pair
+        whenever it is complete and consistent."""
         def __init__(self, device):
             super().__init__(device)
             self.timing = False
+            self.engine = None
             self.ev = {"norm": [], "step": []}
+            self.graph_ev = {}
+            self.graph_ms = {"norm": [], "step": []}
+
+        def sample_graph_events(self):
+            for key, (s, e) in self.graph_ev.items():
+                try:
+                    if e.query():
+                        dt = s.elapsed_time(e)
+                        if 0.0 < dt < 20.0:          # a torn pair (replay in flight) is negative
+                            self.graph_ms[key].append(dt)
+                except Exception:
+                    pass
 
         def _timed(self, key, fn, *a, **k):
+            gp = getattr(self.engine, "graph_pass", None)
+            if gp is not None and gp.mode == "capture":
+                s = torch.cuda.Event(enable_timing=True, external=True)
+                e = torch.cuda.Event(enable_timing=True, external=True)
+                s.record()
+                out = fn(*a, **k)
+                e.record()
+                self.graph_ev[key] = (s, e)
+                return out
             if not self.timing:
                 return fn(*a, **k)
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -222,6 +247,9 @@ def run_ours(args) -> dict:
         def sgd_step(self, *a, **k):
             return self._timed("step", super().sgd_step, *a, **k)
 
+        def step_devtable(self, *a, **k):
+            return self._timed("step", super().step_devtable, *a, **k)
+
         def l2norm_finalize(self, *a, **k):
             return self._timed("norm", super().l2norm_finalize, *a, **k)
 
@@ -231,6 +259,7 @@ def run_ours(args) -> dict:
         dev = torch.device("cuda", local)
         torch.cuda.set_device(dev)
         eng = Engine(backend=TimedBackend(dev), device=dev, **kw)
+        eng.backend.engine = eng
         holder["engine"] = eng
         return eng
 
@@ -273,10 +302,13 @@ def run_ours(args) -> dict:
             be = self._accelerator.backend
             if self.i > W and self.read_loss and attrs.looper.state.loss is not None:
                 self.losses.append(attrs.looper.state.loss)
+            if be.timing:
+                be.sample_graph_events()
             if self.i == W:
                 self._fence()
-                self.launch0 = _native.launch_count()
+                self.launch0 = _native.launch_count() + self._accelerator.replayed_kernel_launches
                 be.timing = True
+                be.graph_ms = {"norm": [], "step": []}
                 for sync in self._accelerator._grad_sync.values():
                     if hasattr(sync, "profile"):
                         sync.profile, self.sync = True, sync
@@ -288,11 +320,13 @@ def run_ours(args) -> dict:
                     self.host_losses = [float(v) for v in self.losses]
                 self.t1.record()
                 self._fence()
+                be.sample_graph_events()
                 be.timing = False
                 if getattr(self, "sync", None) is not None:
                     self.sync.profile = False
                     self.exchange = [(nb, a.elapsed_time(b)) for nb, a, b in self.sync.timings]
-                self.launches = _native.launch_count() - self.launch0
+                self.launches = _native.launch_count() \
+                    + self._accelerator.replayed_kernel_launches - self.launch0
                 self.clocks = self.sampler.stop() if rank == 0 else None
                 self.ms = self.t0.elapsed_time(self.t1)
 
@@ -302,7 +336,7 @@ def run_ours(args) -> dict:
         objective = NextTokenLoss() if WL.get("tokens") else workloads.CrossEntropy()
         inner = [rk.Loss(objective=objective),
                  rk.Optimizer(opt, max_grad_norm=WL["max_norm"])]
-        looper = rk.Looper([data_capsule, rk.Module(net, capsules=inner), probe],
+        looper = rk.Looper([data_capsule, rk.Module(net, capsules=inner, graph=args.graph), probe],
                            tag="bench", repeats=W + K)
         return rk.Launcher([looper], num_epochs=1, mixed_precision=WL["mixed_precision"],
                            gradient_accumulation_steps=WL.get("accum", 1),
@@ -314,8 +348,8 @@ def run_ours(args) -> dict:
     launcher.launch()
     be = holder["engine"].backend
     n_params = sum(p.numel() for p in opt.param_groups[0]["params"])
-    step_ms = [s.elapsed_time(e) for s, e in be.ev["step"]]
-    norm_ms = [s.elapsed_time(e) for s, e in be.ev["norm"]]
+    step_ms = [s.elapsed_time(e) for s, e in be.ev["step"]] + be.graph_ms["step"]
+    norm_ms = [s.elapsed_time(e) for s, e in be.ev["norm"]] + be.graph_ms["norm"]
     ms = torch.tensor([probe.ms], device="cuda")
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -374,6 +408,7 @@ def run_ours(args) -> dict:
                    "global_batch": WL.get("batch", BATCH) * world * WL.get("accum", 1),
                    "parallelism": f"dp{world}",
                    "grad_sync": (holder["engine"].grad_sync_kinds or ["none"])[0],
+                   "cuda_graph_step": bool(args.graph) and world == 1,
                    "l2": "no explicit flush: per-step working set (45 MB x4 optimizer streams "
                          "+ activations of bs 256) exceeds the 126 MB L2",
                    "params": n_params},
@@ -388,7 +423,7 @@ def run_ours(args) -> dict:
                      "frac": round(achieved / peak, 4),
                      "traffic": measured_traffic() if args.workload == "resnet18" else None,
                      "peak_source": peak_src, "algorithmic_bytes_per_param": algo,
-                     "launch_ms": round(k2_ms, 5),
+                     "launch_ms": round(k2_ms, 5), "launches_timed": len(step_ms),
                      "norm_kernel_ms": round(statistics.mean(norm_ms), 5) if norm_ms else None,
                      "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
     }
@@ -569,6 +604,9 @@ def main() -> None:
     ap.add_argument("--no-optstep", action="store_true", help="skip the 1e9-param microbench")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--workload", default="resnet18", choices=list(WORKLOADS))
+    ap.add_argument("--graph", type=int, default=1,
+                    help="Module(graph=...): replay the training step from a CUDA graph (1) or "
+                         "run it eagerly (0)")
     ap.add_argument("--loader-workers", type=int, default=0,
                     help="DataLoader worker processes of the e2e leg (0 = load in-process)")
     args = ap.parse_args()

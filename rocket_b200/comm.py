@@ -167,7 +167,9 @@ class P2PGradSync(_BucketedSync):
         dist.barrier()         # every rank has mapped every arena (and they are zero-filled)
 
     def _can_launch(self) -> bool:
-        return self.opt._plan is not None
+        # While a CUDA graph of the step is being captured the buckets are issued from
+        # finish(), on the capturing thread, instead of from autograd's hook thread.
+        return self.opt._plan is not None and self.engine.graph_pass is None
 
     def _chunk_range(self, b: int) -> tuple[int, int]:
         first, last = self.param_ranges[b]

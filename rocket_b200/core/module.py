@@ -72,8 +72,12 @@ class Module(Dispatcher):
     # ---- CUDA-graph path (graph=True) ---------------------------------------------------
     def _graphable(self) -> bool:
         engine = self._accelerator
-        return engine.device.type == "cuda" and hasattr(engine, "graph_pass") \
-            and engine.num_processes == 1
+        if engine.device.type != "cuda" or not hasattr(engine, "graph_pass"):
+            return False
+        # multi-GPU: only the hand-written NVLink exchange is replayable (device-side epochs)
+        return engine.num_processes == 1 or (
+            bool(engine.grad_sync_kinds)
+            and all(k == "P2PGradSync" for k in engine.grad_sync_kinds))
 
     def _launch_graphed(self, attrs: Attributes) -> None:
         from rocket_b200.engine import GraphPass
@@ -93,6 +97,7 @@ class Module(Dispatcher):
             for dst, src in zip(step.inputs, leaves):
                 dst.copy_(src)
             engine.graph_pass = gp = GraphPass("capture", step.slots)
+            launches_before = engine.backend.launch_count()
             try:
                 torch.cuda.synchronize(engine.device)
                 with torch.cuda.graph(step.graph, capture_error_mode="thread_local"):
@@ -101,6 +106,8 @@ class Module(Dispatcher):
                     Dispatcher.launch(self, attrs=attrs)
             finally:
                 engine.graph_pass = None
+            # how many of the engine's kernels one replay of this graph runs
+            step.kernel_launches = engine.backend.launch_count() - launches_before
             self._graphs[key] = step
         else:
             for dst, src in zip(step.inputs, leaves):
@@ -114,6 +121,7 @@ class Module(Dispatcher):
         for action in gp.pre:
             action()
         step.graph.replay()
+        engine.replayed_kernel_launches += step.kernel_launches
         for action in gp.post:
             action()
 
@@ -149,6 +157,7 @@ class _CapturedStep:
         self.inputs = inputs
         self.outputs = None
         self.slots: dict = {}
+        self.kernel_launches = 0
 
 
 class _Leaf:

@@ -34,6 +34,9 @@ struct CommSignals {
   unsigned long long ready[RK_COMM_MAX_BUCKETS][RK_COMM_MAX_WORLD];
   unsigned long long done[RK_COMM_MAX_BUCKETS][RK_COMM_MAX_WORLD];
   unsigned int arrived[RK_COMM_MAX_BUCKETS];
+  // how many times each bucket has been exchanged; kept on the device (not passed as a launch
+  // argument) so that a kernel replayed from a CUDA graph still gets a fresh epoch every time
+  unsigned long long epoch[RK_COMM_MAX_BUCKETS];
 };
 static_assert(sizeof(CommSignals) <= RK_COMM_SIGNAL_BYTES, "signal pad too small");
 
@@ -86,12 +89,13 @@ template <int W, bool MC>
 __global__ void __launch_bounds__(COMM_THREADS)
 rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
                          const char* __restrict__ plan, unsigned long long scratch_off,
-                         int chunk_lo, int chunk_hi, int bucket, float scale,
-                         unsigned long long epoch) {
+                         int chunk_lo, int chunk_hi, int bucket, float scale) {
   __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   __shared__ double s_red[2][COMM_WARPS];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   CommSignals* mine = reinterpret_cast<CommSignals*>(peers.arena[rank]);
+  // every CTA reads the same value: it is only advanced by the last CTA, after all arrived
+  const unsigned long long epoch = mine->epoch[bucket] + 1;
 
   // ---- start barrier ---------------------------------------------------------------
   if (blockIdx.x == 0 && tid < W)
@@ -241,6 +245,7 @@ rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
     const unsigned int prev = atomicAdd(&mine->arrived[bucket], 1u);
     if (prev == gridDim.x - 1) {
       mine->arrived[bucket] = 0u;
+      mine->epoch[bucket] = epoch;
       __threadfence_system();
       for (int q = 0; q < W; ++q)
         st_release_sys(&reinterpret_cast<CommSignals*>(peers.arena[q])->done[bucket][rank], epoch);
@@ -256,7 +261,6 @@ struct rk_comm {
   CommPeers peers;
   char* mc_arena;   // multicast mapping of all arenas, or nullptr
   unsigned long long scratch_off;
-  unsigned long long epoch[RK_COMM_MAX_BUCKETS];
 };
 
 extern "C" int rk_comm_create(rk_comm** out, int rank, int world, void* const* arenas,
@@ -281,7 +285,6 @@ extern "C" int rk_comm_create(rk_comm** out, int rank, int world, void* const* a
     }
     c->peers.arena[q] = (char*)arenas[q];
   }
-  for (int b = 0; b < RK_COMM_MAX_BUCKETS; ++b) c->epoch[b] = 0;
   cudaError_t e = cudaGetDevice(&c->device);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, c->device);
   if (e != cudaSuccess) {
@@ -309,13 +312,12 @@ extern "C" int rk_comm_allreduce_norm(rk_comm* c, const void* plan_host, const v
   int grid = max_ctas > 0 ? max_ctas : c->sms;
   if (grid > owned) grid = owned;
   if (grid < 1) grid = 1;   // still takes part in both barriers
-  const unsigned long long epoch = ++c->epoch[bucket];
   const float scale = 1.0f / (float)W;
   cudaStream_t s = (cudaStream_t)stream;
   const bool mc = c->mc_arena != nullptr && use_multicast != 0;
 #define RK_LAUNCH(WW, MC)                                                                    \
   rk_allreduce_norm_kernel<WW, MC><<<grid, COMM_THREADS, 0, s>>>(c->peers, c->mc_arena,      \
-      c->rank, (const char*)plan_dev, c->scratch_off, chunk_lo, chunk_hi, bucket, scale, epoch)
+      c->rank, (const char*)plan_dev, c->scratch_off, chunk_lo, chunk_hi, bucket, scale)
   switch (W) {
     case 2: if (mc) RK_LAUNCH(2, true); else RK_LAUNCH(2, false); break;
     case 4: if (mc) RK_LAUNCH(4, true); else RK_LAUNCH(4, false); break;

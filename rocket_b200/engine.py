@@ -211,6 +211,7 @@ class Engine:
         self._bucket_cap_mb = bucket_cap_mb
         self._p2p = None
         self.graph_pass: GraphPass | None = None    # set by Module(graph=True) around a pass
+        self.replayed_kernel_launches = 0           # engine kernels run by graph replays
         self.grad_sync_kinds: list[str] = []      # which exchange each optimizer got
         self.stager = None
         if self.device.type == "cuda" and stage_batches:

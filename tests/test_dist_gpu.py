@@ -25,7 +25,7 @@ GOLDEN = Path(__file__).parent / "golden"
 
 
 def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str,
-                sync: str = "p2p") -> None:
+                sync: str = "p2p", graph: bool = False) -> None:
     os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
                       MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), TQDM_DISABLE="1",
                       ROCKET_B200_GRAD_SYNC=sync)
@@ -46,10 +46,13 @@ def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str,
     kw = dict(dist_worker.WS2_CASES[case])
     launcher, h = workloads.build_mnist_graph(
         rk, tracker_backend=tracker, clip_via="kwarg" if kw["max_norm"] else "capsule",
-        accuracy_cls=Accuracy, **kw)
+        accuracy_cls=Accuracy, graph=graph, **kw)
     launcher.launch()
+    if graph:
+        assert len(launcher._capsules[0]._capsules[1]._graphs) >= 1, "no step was captured"
+        sync = "p2p_graph"
     # the path under test really ran (no silent fall back to the other exchange)
-    assert engines[0].grad_sync_kinds == ["P2PGradSync" if sync == "p2p" else "GradSync"], \
+    assert engines[0].grad_sync_kinds == ["GradSync" if sync == "nccl" else "P2PGradSync"], \
         engines[0].grad_sync_kinds
     np.savez_compressed(Path(out_dir) / f"{case}_{sync}_rank{rank}.npz",
                         **dist_worker._collect(h, tracker))
@@ -91,6 +94,25 @@ def test_fused_nvlink_allreduce_equals_nccl_path_bitwise(tmp_path):
     for k in a.files:
         if k.startswith("param/"):
             assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), k
+    assert a["loss_values"].tolist() == b["loss_values"].tolist()
+    assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_graph_captured_step_with_nvlink_exchange_equals_eager(tmp_path):
+    """Module(graph=True) on two GPUs: the fused NVLink exchange kernels (device-side epochs),
+    the NCCL loss reduction and the optimizer step are nodes of the replayed graph; results
+    must equal the eager two-GPU run bit for bit."""
+    case = "ws2_adamw_clip"
+    mp.spawn(_gpu_worker, args=(2, 29860, case, str(tmp_path), "p2p", False), nprocs=2, join=True)
+    mp.spawn(_gpu_worker, args=(2, 29861, case, str(tmp_path), "p2p", True), nprocs=2, join=True)
+    a = np.load(tmp_path / f"{case}_p2p_rank0.npz")
+    b = np.load(tmp_path / f"{case}_p2p_graph_rank0.npz")
+    c = np.load(tmp_path / f"{case}_p2p_graph_rank1.npz")
+    for k in a.files:
+        if k.startswith("param/"):
+            assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), k
+            assert np.array_equal(b[k].view(np.int32), c[k].view(np.int32)), k
     assert a["loss_values"].tolist() == b["loss_values"].tolist()
     assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
 
