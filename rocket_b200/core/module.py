@@ -37,6 +37,7 @@ class Module(Dispatcher):
         self._graph = graph
         self._graphs: dict = {}      # signature -> _CapturedStep
         self._warm: dict = {}        # signature -> eager iterations seen
+        self.graphs_captured = 0     # how many step graphs this capsule has captured
 
     def setup(self, attrs: Attributes | None = None) -> None:
         self.check_accelerator()
@@ -109,6 +110,7 @@ class Module(Dispatcher):
             # how many of the engine's kernels one replay of this graph runs
             step.kernel_launches = engine.backend.launch_count() - launches_before
             self._graphs[key] = step
+            self.graphs_captured += 1
         else:
             for dst, src in zip(step.inputs, leaves):
                 dst.copy_(src)
@@ -126,6 +128,14 @@ class Module(Dispatcher):
             action()
 
     def destroy(self, attrs: Attributes | None = None) -> None:
+        if self._graphs:
+            # Captured steps hold NCCL / NVLink-exchange kernels and pool memory: release them
+            # while the process group and the peers' mappings are still alive (a graph that
+            # outlives them hangs the interpreter at exit).
+            if self._accelerator.device.type == "cuda":
+                torch.cuda.synchronize(self._accelerator.device)
+            self._graphs.clear()
+            self._warm.clear()
         models = self._accelerator._models
         for i, model in enumerate(models):
             if model is self._module:
