@@ -354,11 +354,6 @@ class Engine:
         if sync is not None:
             sync.step_done()
 
-    def note_late_gradient(self, opt) -> None:
-        """A gradient was adopted into the flat buffer after backward: its bucket has not
-        been reduced by a hook; GradSync.finish() launches it."""
-        return None
-
     def clip_grad_norm_(self, parameters=None, max_norm: float = 1.0, norm_type: float = 2.0):
         """Global-norm clipping for user capsules (accelerate: ``clip_grad_norm_``).  The
         coefficient is applied inside the next fused step; returns the device norm."""

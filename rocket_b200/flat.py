@@ -231,7 +231,6 @@ class EngineOptimizer:
                                           scale, True)
         eng.grad_sync_step_done(self)
         self._zeroed_by_step = True
-        self._state_dirty = True
         self.optimizer._opt_called = True   # what torch's LRScheduler checks before warning
 
     def _step_groups(self) -> list[dict]:
@@ -301,7 +300,6 @@ class EngineOptimizer:
                     raise NotImplementedError("sparse gradients are not supported")
                 self._views_g[i].copy_(g)
                 p.grad = self._views_g[i]
-                self.engine.note_late_gradient(self)
             if not self._adopted[i]:
                 self._adopted[i] = True
                 changed = True
@@ -322,8 +320,6 @@ class EngineOptimizer:
         return self._plan
 
     # ---- state in torch's own format (checkpoints) ----------------------------------------------------
-    _state_dirty = False
-
     def _export_state(self) -> None:
         for i, p in enumerate(self._params):
             if not self._adopted[i]:
@@ -337,7 +333,6 @@ class EngineOptimizer:
             else:
                 st["step"] = torch.tensor(float(step), dtype=torch.float32)
                 st["exp_avg"], st["exp_avg_sq"] = self._views_m[i], self._views_v[i]
-        self._state_dirty = False
 
     def state_dict(self) -> dict:
         self._export_state()
