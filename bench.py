@@ -511,9 +511,11 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
     be = NativeBackend(dev)
     sig = N.RK_COMM_SIGNAL_BYTES
     scratch = -(-be.scratch_bytes([n]) // 256) * 256
-    arena = alloc_arena(sig + scratch + 4 * n, dev)
-    g = arena[sig + scratch:].view(torch.float32)
-    p = torch.randn(n, device=dev) * 0.02
+    arena = alloc_arena(sig + scratch + 8 * n, dev)       # [signals | scratch | g | p]
+    g = arena[sig + scratch:sig + scratch + 4 * n].view(torch.float32)
+    p = arena[sig + scratch + 4 * n:].view(torch.float32)
+    torch.manual_seed(5)
+    p.normal_(0, 0.02)
     m = torch.zeros(n, device=dev)
     v = torch.zeros(n, device=dev)
     plan = be.make_plan([TensorSpec(p=p, g=g, m=m, v=v, group=0)], scratch=arena[sig:sig + scratch])
@@ -544,9 +546,36 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
         if i >= warmup:
             tx.append(e[0].elapsed_time(e[1]))
             ts.append(e[1].elapsed_time(e[2]))
-    t = torch.tensor([statistics.mean(tx), statistics.mean(ts)], device=dev)
+    # the same step with the optimizer sharded: reduce-scatter (+ norm), then every rank
+    # updates the 1/W of the chunks it owns and writes the new parameters to all ranks
+    table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8, device=dev)
+    host_table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8).pin_memory()
+    m.zero_()
+    v.zero_()
+    sx, ss = [], []
+    for i in range(warmup + steps):
+        torch.manual_seed(1000 * i + rank)
+        g.normal_(0, 1e-3)
+        be.step_table_write("adamw", [dict(hp, step=i + 1)], host_table)
+        table.copy_(host_table, non_blocking=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
+        be.comm_reduce_scatter_norm(comm, plan, 0, plan.n_chunks_norm, 0, 74 if use_mc else 0,
+                                    stream, use_mc)
+        norm = be.l2norm_finalize(plan)
+        e[1].record()
+        be.comm_sharded_step(comm, plan, "adamw", table.data_ptr(), norm, 1.0, 0, use_mc)
+        e[2].record()
+        torch.cuda.synchronize()
+        if i >= warmup:
+            sx.append(e[0].elapsed_time(e[1]))
+            ss.append(e[1].elapsed_time(e[2]))
+    t = torch.tensor([statistics.mean(tx), statistics.mean(ts), statistics.mean(sx),
+                      statistics.mean(ss)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    t_x, t_s = float(t[0]), float(t[1])
+    t_x, t_s, s_x, s_s = (float(x) for x in t)
     dist.barrier()
     be.comm_destroy(comm)
     del keep, p, m, v, g, plan, arena
@@ -559,6 +588,9 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
             "step_kernel_ms": round(t_s, 4),
             "step_kernel_gbs": round(ALGO_BYTES_STEP * n / (t_s * 1e-3) / 1e9, 1),
             "ms_per_optimizer_step": round(t_x + t_s, 4),
+            "sharded": {"reduce_scatter_plus_norm_ms": round(s_x, 4),
+                        "sharded_step_ms": round(s_s, 4),
+                        "ms_per_optimizer_step": round(s_x + s_s, 4)},
             "step_kernel_frac_of_measured_peak":
                 round(ALGO_BYTES_STEP * n / (t_s * 1e-3) / 1e9 / peak, 4)}
 

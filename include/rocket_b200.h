@@ -246,6 +246,30 @@ int rk_comm_allreduce_norm(rk_comm* comm, const void* plan_host, const void* pla
                            int use_multicast, void* stream);
 int rk_comm_destroy(rk_comm* comm);
 
+/* ---- K7: sharded optimizer step -----------------------------------
+ * The reference has no counterpart: under DDP every replica repeats the whole
+ * torch.optim step (rocket/core/optimizer.py:129).  Here the arena additionally carries the
+ * parameters   [ signal pad | norm scratch | gradients | parameters ]   and rank r owns the
+ * norm chunks c with c % W == r, the same ownership as the exchange.
+ * rk_comm_reduce_scatter_norm is rk_comm_allreduce_norm without the broadcast half: the owner
+ * alone keeps sum_r(g_r) * (1/W) of its chunks (other ranks' copies of those chunks stay as
+ * they were); the norm partials still reach every rank.
+ * rk_comm_sharded_step then applies rk_adamw_step_multi_devtable's (optimizer 0) or
+ * rk_sgd_step_multi_devtable's (optimizer 1) element update to the owned chunks only, writes
+ * the new parameters into every rank's arena (P2P stores / multimem.st), keeps m and v local,
+ * zero-fills the whole local gradient buffer, and ends with a barrier among the ranks.  Per
+ * element the arithmetic is the replicated step's, so parameters are bit-identical to data
+ * parallelism; optimizer work and moment traffic per GPU shrink by W.  table_dev is the
+ * RK_STEP_TABLE_BYTES table written by rk_adam_table_write / rk_sgd_table_write; the m / v
+ * pointers of chunks a rank does not own are never touched.  Uses barrier slot
+ * RK_COMM_MAX_BUCKETS - 1: exchanges that share the communicator must use lower buckets.  */
+int rk_comm_reduce_scatter_norm(rk_comm* comm, const void* plan_host, const void* plan_dev,
+                                int chunk_lo, int chunk_hi, int bucket, int max_ctas,
+                                int use_multicast, void* stream);
+int rk_comm_sharded_step(rk_comm* comm, const void* plan_host, const void* plan_dev,
+                         int optimizer, const void* table_dev, const float* total_norm_dev,
+                         float max_norm, int max_ctas, int use_multicast, void* stream);
+
 /* ---- K5: pinned-ring batch stager ---------------------------------------------------
  * Replaces the blocking pageable `Tensor.to(device)` of rocket/utils/torch.py:50-51
  * reached from rocket/core/dataset.py:279-282.  The caller supplies a pinned host ring

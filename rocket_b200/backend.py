@@ -124,6 +124,23 @@ class NativeBackend:
                                                 int(use_multicast), stream),
                 "rk_comm_allreduce_norm")
 
+    def comm_reduce_scatter_norm(self, comm, plan: Plan, chunk_lo: int, chunk_hi: int,
+                                 bucket: int, max_ctas: int, stream: int,
+                                 use_multicast: bool = True) -> None:
+        N.check(self.lib.rk_comm_reduce_scatter_norm(
+            comm, plan.host.data_ptr(), plan.dev.data_ptr(), chunk_lo, chunk_hi, bucket,
+            max_ctas, int(use_multicast), stream), "rk_comm_reduce_scatter_norm")
+
+    # K7
+    def comm_sharded_step(self, comm, plan: Plan, kind: str, table_dev_ptr: int,
+                          total_norm=None, max_norm: float = 0.0, max_ctas: int = 0,
+                          use_multicast: bool = True) -> None:
+        N.check(self.lib.rk_comm_sharded_step(
+            comm, plan.host.data_ptr(), plan.dev.data_ptr(), 1 if kind == "sgd" else 0,
+            table_dev_ptr, total_norm.data_ptr() if total_norm is not None else None,
+            float(max_norm), max_ctas, int(use_multicast), self._stream()),
+            "rk_comm_sharded_step")
+
     def comm_destroy(self, comm) -> None:
         self.lib.rk_comm_destroy(comm)
 

@@ -146,8 +146,11 @@ class P2PGradSync(_BucketedSync):
 
     def __init__(self, opt, engine, bucket_cap_mb: float = 32.0):
         super().__init__(opt, engine, bucket_cap_mb)
-        if len(self.buckets) > 256:
-            raise NotImplementedError("more than 256 gradient buckets")
+        # reduce-scatter instead of all-reduce when the optimizer step is sharded: the owner
+        # alone needs the averaged chunk, everybody gets the new parameters instead
+        self.broadcast = not opt.sharded
+        if len(self.buckets) > 256 - int(opt.sharded):     # the sharded step's barrier slot
+            raise NotImplementedError("more than 255 gradient buckets")
         self.backend = engine.backend
         self.max_ctas = int(os.environ.get("ROCKET_B200_COMM_CTAS", "0"))
         self.stream = torch.cuda.Stream(device=engine.device)
@@ -161,6 +164,7 @@ class P2PGradSync(_BucketedSync):
             want_mc == "1" or (want_mc == "auto" and engine.num_processes >= 4))
         if self.use_multicast and self.max_ctas == 0:
             self.max_ctas = 74      # the switch does the work: half the SMs issue enough
+        self.step_ctas = int(os.environ.get("ROCKET_B200_SHARDED_STEP_CTAS", "0"))
         self._comm = self.backend.comm_create(
             engine.process_index, engine.num_processes, ptrs, opt._scratch_offset,
             self.multicast_ptr)
@@ -186,8 +190,10 @@ class P2PGradSync(_BucketedSync):
         if self.profile:
             t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             t0.record(self.stream)
-        self.backend.comm_allreduce_norm(self._comm, plan, lo, hi, b, self.max_ctas,
-                                         self.stream.cuda_stream, self.use_multicast)
+        exchange = self.backend.comm_allreduce_norm if self.broadcast \
+            else self.backend.comm_reduce_scatter_norm
+        exchange(self._comm, plan, lo, hi, b, self.max_ctas, self.stream.cuda_stream,
+                 self.use_multicast)
         if self.profile:
             t1.record(self.stream)
             self.timings.append(((e1 - e0) * 4, t0, t1))

@@ -1,8 +1,9 @@
 """Optimizer capsule: the fused step.
 
-API mirror of the reference's rocket/core/optimizer.py:21-204, plus ONE additive keyword,
+API mirror of the reference's rocket/core/optimizer.py:21-204, plus two additive keywords:
 ``max_grad_norm`` (default ``None`` = the reference's behaviour: it has no clipping at all,
-SURVEY.md section 0.5).  The reference's ``step(); zero_grad()`` (optimizer.py:129-130)
+SURVEY.md section 0.5) and ``sharded`` (default ``None`` = replicated step, as under DDP;
+``True`` = each rank updates 1/W of the parameters, Engine.prepare_optimizer).  The reference's ``step(); zero_grad()`` (optimizer.py:129-130)
 reaches torch.optim's per-tensor loops; here the prepared optimizer runs, on sync steps,
 one deterministic norm kernel (if clipping) and one fused multi-tensor kernel that applies
 1/world_size, the clip coefficient, the AdamW/SGD update and the gradient zero-fill in a
@@ -18,12 +19,14 @@ from rocket_b200.core.capsule import Attributes, Capsule
 
 class Optimizer(Capsule):
     def __init__(self, optimizer: torch.optim.Optimizer, tag: str = "opt",
-                 priority: int = 1000, max_grad_norm: float | None = None) -> None:
+                 priority: int = 1000, max_grad_norm: float | None = None,
+                 sharded: bool | None = None) -> None:
         super().__init__(statefull=False, priority=priority)
         self._optimizer = optimizer
         self._tag = tag
         self._iter_idx = 0
         self._max_grad_norm = max_grad_norm
+        self._sharded = sharded
 
     def setup(self, attrs: Attributes | None = None) -> None:
         Capsule.setup(self, attrs=attrs)
@@ -37,7 +40,11 @@ class Optimizer(Capsule):
             found = True
             self._optimizer = prepared
         if not found:
-            self._optimizer = self._accelerator.prepare(self._optimizer)
+            if self._sharded is None:
+                self._optimizer = self._accelerator.prepare(self._optimizer)
+            else:
+                self._optimizer = self._accelerator.prepare_optimizer(self._optimizer,
+                                                                      sharded=self._sharded)
         if self._max_grad_norm is not None:
             self._optimizer.max_grad_norm = float(self._max_grad_norm)
 

@@ -20,6 +20,7 @@
 // as seen from this rank.  Cross-GPU flags carry a monotonically increasing epoch, so they
 // never need resetting.
 #include "rk_common.cuh"
+#include "rk_step_ops.cuh"
 
 #define COMM_THREADS 256
 #define COMM_WARPS (COMM_THREADS / 32)
@@ -89,7 +90,10 @@ template <int W, bool MC>
 __global__ void __launch_bounds__(COMM_THREADS)
 rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
                          const char* __restrict__ plan, unsigned long long scratch_off,
-                         int chunk_lo, int chunk_hi, int bucket, float scale) {
+                         int chunk_lo, int chunk_hi, int bucket, float scale, int broadcast) {
+  // broadcast != 0: all-reduce (every rank receives every averaged chunk).
+  // broadcast == 0: reduce-scatter (only the owner keeps its averaged chunks; used by the
+  //                 sharded optimizer step, which broadcasts parameters instead).
   __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   __shared__ double s_red[2][COMM_WARPS];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -145,7 +149,8 @@ rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
                 s[k].z = __fmul_rn(s[k].z, scale); s[k].w = __fmul_rn(s[k].w, scale);
                 a0 = fmaf(s[k].x, s[k].x, a0); a1 = fmaf(s[k].y, s[k].y, a1);
                 a2 = fmaf(s[k].z, s[k].z, a2); a3 = fmaf(s[k].w, s[k].w, a3);
-                mc_st4(m + 4 * i, s[k]);
+                if (broadcast) mc_st4(m + 4 * i, s[k]);
+                else st_peer4(reinterpret_cast<float*>(peers.arena[rank] + off) + 4 * i, s[k]);
               }
             }
           }
@@ -153,13 +158,15 @@ rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
           if (i < count) {
             const float v = __fmul_rn(mc_ld_reduce1(m + i), scale);
             a0 = fmaf(v, v, a0);
-            mc_st1(m + i, v);
+            if (broadcast) mc_st1(m + i, v);
+            else reinterpret_cast<float*>(peers.arena[rank] + off)[i] = v;
           }
         } else {
           for (int i = tid; i < count; i += COMM_THREADS) {
             const float v = __fmul_rn(mc_ld_reduce1(m + i), scale);
             a0 = fmaf(v, v, a0);
-            mc_st1(m + i, v);
+            if (broadcast) mc_st1(m + i, v);
+            else reinterpret_cast<float*>(peers.arena[rank] + off)[i] = v;
           }
         }
       } else {
@@ -195,7 +202,8 @@ rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
                 a0 = fmaf(s.x, s.x, a0); a1 = fmaf(s.y, s.y, a1);
                 a2 = fmaf(s.z, s.z, a2); a3 = fmaf(s.w, s.w, a3);
   #pragma unroll
-                for (int q = 0; q < W; ++q) st_peer4(g[q] + 4 * i, s);
+                for (int q = 0; q < W; ++q)
+                  if (broadcast || q == rank) st_peer4(g[q] + 4 * i, s);
               }
             }
           }
@@ -207,7 +215,8 @@ rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
             s = __fmul_rn(s, scale);
             a0 = fmaf(s, s, a0);
   #pragma unroll
-            for (int q = 0; q < W; ++q) g[q][i] = s;
+            for (int q = 0; q < W; ++q)
+              if (broadcast || q == rank) g[q][i] = s;
           }
         } else {
           for (int i = tid; i < count; i += COMM_THREADS) {
@@ -217,7 +226,8 @@ rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
             s = __fmul_rn(s, scale);
             a0 = fmaf(s, s, a0);
   #pragma unroll
-            for (int q = 0; q < W; ++q) g[q][i] = s;
+            for (int q = 0; q < W; ++q)
+              if (broadcast || q == rank) g[q][i] = s;
           }
         }
       }
@@ -296,9 +306,9 @@ extern "C" int rk_comm_create(rk_comm** out, int rank, int world, void* const* a
   return 0;
 }
 
-extern "C" int rk_comm_allreduce_norm(rk_comm* c, const void* plan_host, const void* plan_dev,
-                                      int chunk_lo, int chunk_hi, int bucket, int max_ctas,
-                                      int use_multicast, void* stream) {
+static int launch_exchange(rk_comm* c, const void* plan_host, const void* plan_dev, int chunk_lo,
+                           int chunk_hi, int bucket, int max_ctas, int use_multicast,
+                           int broadcast, void* stream) {
   RK_REQUIRE(c && plan_host && plan_dev, RK_ERR_INVALID, "rk_comm_allreduce_norm: null argument");
   const rk_plan_header* h = (const rk_plan_header*)plan_host;
   RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "rk_comm_allreduce_norm: bad plan magic");
@@ -317,7 +327,8 @@ extern "C" int rk_comm_allreduce_norm(rk_comm* c, const void* plan_host, const v
   const bool mc = c->mc_arena != nullptr && use_multicast != 0;
 #define RK_LAUNCH(WW, MC)                                                                    \
   rk_allreduce_norm_kernel<WW, MC><<<grid, COMM_THREADS, 0, s>>>(c->peers, c->mc_arena,      \
-      c->rank, (const char*)plan_dev, c->scratch_off, chunk_lo, chunk_hi, bucket, scale)
+      c->rank, (const char*)plan_dev, c->scratch_off, chunk_lo, chunk_hi, bucket, scale,    \
+      broadcast)
   switch (W) {
     case 2: if (mc) RK_LAUNCH(2, true); else RK_LAUNCH(2, false); break;
     case 4: if (mc) RK_LAUNCH(4, true); else RK_LAUNCH(4, false); break;
@@ -327,6 +338,189 @@ extern "C" int rk_comm_allreduce_norm(rk_comm* c, const void* plan_host, const v
   RK_CUDA(cudaGetLastError());
   g_rk_launches.fetch_add(1);
   return 0;
+}
+
+extern "C" int rk_comm_allreduce_norm(rk_comm* c, const void* plan_host, const void* plan_dev,
+                                      int chunk_lo, int chunk_hi, int bucket, int max_ctas,
+                                      int use_multicast, void* stream) {
+  return launch_exchange(c, plan_host, plan_dev, chunk_lo, chunk_hi, bucket, max_ctas,
+                         use_multicast, /*broadcast=*/1, stream);
+}
+
+extern "C" int rk_comm_reduce_scatter_norm(rk_comm* c, const void* plan_host,
+                                           const void* plan_dev, int chunk_lo, int chunk_hi,
+                                           int bucket, int max_ctas, int use_multicast,
+                                           void* stream) {
+  return launch_exchange(c, plan_host, plan_dev, chunk_lo, chunk_hi, bucket, max_ctas,
+                         use_multicast, /*broadcast=*/0, stream);
+}
+
+// ---- sharded optimizer step ------------------------------------------------------------
+// After rk_comm_reduce_scatter_norm every rank holds the averaged gradient of the norm chunks
+// it owns (c % W == rank).  This kernel walks ALL chunks: an owned chunk gets the fused
+// AdamW / SGD update on the local p, g, m, v and its new parameters are written into every
+// rank's parameter buffer (P2P stores, or one multimem.st that the switch replicates); any
+// other chunk only has its local gradient zero-filled.  Optimizer work and moment traffic per
+// GPU shrink by W; per element the arithmetic is the replicated step's, so the result is
+// bit-identical to data parallelism.  One end barrier: nobody's next forward may start
+// before all owners' parameters have landed.
+template <class Op, class Table, int W, bool MC>
+__global__ void __launch_bounds__(COMM_THREADS, 3)
+rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
+                       const char* __restrict__ plan, const Table* __restrict__ dtable,
+                       const float* __restrict__ total_norm, float max_norm, int bucket) {
+  __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
+  const int tid = threadIdx.x;
+  CommSignals* mine = reinterpret_cast<CommSignals*>(peers.arena[rank]);
+  const unsigned long long epoch = mine->epoch[bucket] + 1;
+  const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
+  const int n_tensors = h->n_tensors;
+  const int n_chunks = h->n_chunks_norm;
+  const int chunk = h->chunk_norm;
+  const rk_tensor_desc* descs = reinterpret_cast<const rk_tensor_desc*>(plan + h->off_descs);
+  const int32_t* prefix = rk_stage_prefix(
+      reinterpret_cast<const int32_t*>(plan + h->off_prefix_norm), n_tensors + 1, s_prefix);
+  Prolog pr;
+  pr.scale = 1.0f;
+  pr.has_scale = 0;
+  pr.has_clip = total_norm != nullptr;
+  pr.coef = pr.has_clip ? rk_clip_coef(__ldg(total_norm), max_norm) : 1.0f;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+    const int t = rk_find_tensor(prefix, n_tensors, c);
+    const rk_tensor_desc d = descs[t];
+    Op op;
+    op.h = dtable->g[d.group];
+    if ((d.flags & RK_TENSOR_SKIP) || (op.h.flags & GROUP_SKIP)) continue;
+    const int64_t base = (int64_t)(c - prefix[t]) * chunk;
+    const int64_t rem = d.numel - base;
+    const int count = rem < chunk ? (int)rem : chunk;
+    float* P = d.p + base;
+    float* G = d.g + base;
+    const bool vec = (d.flags & RK_TENSOR_VEC4) != 0;
+    if (c % W != rank) {                     // not mine: only clear my local gradient
+      if (vec) {
+        const int nvec = count >> 2;
+        for (int i = tid; i < nvec; i += COMM_THREADS) stg4<0>(G + 4 * i, zero4);
+        const int i = (nvec << 2) + tid;
+        if (i < count) stg1(G + i, 0.f);
+      } else {
+        for (int i = tid; i < count; i += COMM_THREADS) stg1(G + i, 0.f);
+      }
+      continue;
+    }
+    float* M = d.m + base;
+    float* V = Op::kHasV ? d.v + base : nullptr;
+    const bool has_m = d.m != nullptr;
+    const unsigned long long poff =
+        (unsigned long long)(reinterpret_cast<char*>(P) - peers.arena[rank]);
+    auto put_p4 = [&](int i, const float4& v) {
+      if constexpr (MC) {
+        mc_st4(reinterpret_cast<float*>(mc_arena + poff) + 4 * i, v);
+      } else {
+#pragma unroll
+        for (int q = 0; q < W; ++q)
+          st_peer4(reinterpret_cast<float*>(peers.arena[q] + poff) + 4 * i, v);
+      }
+    };
+    auto put_p1 = [&](int i, float v) {
+      if constexpr (MC) {
+        mc_st1(reinterpret_cast<float*>(mc_arena + poff) + i, v);
+      } else {
+#pragma unroll
+        for (int q = 0; q < W; ++q) reinterpret_cast<float*>(peers.arena[q] + poff)[i] = v;
+      }
+    };
+    auto one = [&](int i) {
+      float p = ldg1(P + i), m = has_m ? ldg1(M + i) : 0.f, v = Op::kHasV ? ldg1(V + i) : 0.f;
+      op(p, prolog_g(ldg1(G + i), pr), m, v);
+      put_p1(i, p);
+      if (has_m) stg1(M + i, m);
+      if (Op::kHasV) stg1(V + i, v);
+      stg1(G + i, 0.f);
+    };
+    if (vec) {
+      const int nvec = count >> 2;
+      for (int i = tid; i < nvec; i += COMM_THREADS) {
+        float4 p4 = ldg4<1>(P + 4 * i), g4 = ldg4<1>(G + 4 * i), m4 = zero4, v4 = zero4;
+        if (has_m) m4 = ldg4<1>(M + 4 * i);
+        if (Op::kHasV) v4 = ldg4<1>(V + 4 * i);
+        op(p4.x, prolog_g(g4.x, pr), m4.x, v4.x);
+        op(p4.y, prolog_g(g4.y, pr), m4.y, v4.y);
+        op(p4.z, prolog_g(g4.z, pr), m4.z, v4.z);
+        op(p4.w, prolog_g(g4.w, pr), m4.w, v4.w);
+        put_p4(i, p4);
+        if (has_m) stg4<0>(M + 4 * i, m4);
+        if (Op::kHasV) stg4<0>(V + 4 * i, v4);
+        stg4<0>(G + 4 * i, zero4);
+      }
+      const int i = (nvec << 2) + tid;
+      if (i < count) one(i);
+    } else {
+      for (int i = tid; i < count; i += COMM_THREADS) one(i);
+    }
+  }
+
+  // ---- end barrier: all owners' parameters are in place everywhere ------------------------
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned int prev = atomicAdd(&mine->arrived[bucket], 1u);
+    if (prev == gridDim.x - 1) {
+      mine->arrived[bucket] = 0u;
+      mine->epoch[bucket] = epoch;
+      __threadfence_system();
+      for (int q = 0; q < W; ++q)
+        st_release_sys(&reinterpret_cast<CommSignals*>(peers.arena[q])->done[bucket][rank], epoch);
+      for (int q = 0; q < W; ++q)
+        while (ld_acquire_sys(&mine->done[bucket][q]) < epoch) { }
+      __threadfence_system();
+    }
+  }
+}
+
+template <class Op, class Table>
+static int launch_sharded(rk_comm* c, const void* plan_host, const void* plan_dev,
+                          const void* table_dev, const float* total_norm_dev, float max_norm,
+                          int max_ctas, int use_multicast, void* stream) {
+  RK_REQUIRE(c && plan_host && plan_dev && table_dev, RK_ERR_INVALID,
+             "rk_comm_sharded_step: null argument");
+  const rk_plan_header* h = (const rk_plan_header*)plan_host;
+  RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "rk_comm_sharded_step: bad plan magic");
+  int grid = max_ctas > 0 ? max_ctas : 3 * c->sms;
+  if (grid > h->n_chunks_norm) grid = h->n_chunks_norm;
+  if (grid < 1) grid = 1;
+  const int bucket = RK_COMM_MAX_BUCKETS - 1;   // this kernel's own barrier slot
+  const bool mc = c->mc_arena != nullptr && use_multicast != 0;
+  cudaStream_t s = (cudaStream_t)stream;
+#define RK_LAUNCH(WW, MC)                                                                     \
+  rk_sharded_step_kernel<Op, Table, WW, MC><<<grid, COMM_THREADS, 0, s>>>(                   \
+      c->peers, c->mc_arena, c->rank, (const char*)plan_dev, (const Table*)table_dev,         \
+      total_norm_dev, max_norm, bucket)
+  switch (c->world) {
+    case 2: if (mc) RK_LAUNCH(2, true); else RK_LAUNCH(2, false); break;
+    case 4: if (mc) RK_LAUNCH(4, true); else RK_LAUNCH(4, false); break;
+    case 8: if (mc) RK_LAUNCH(8, true); else RK_LAUNCH(8, false); break;
+  }
+#undef RK_LAUNCH
+  RK_CUDA(cudaGetLastError());
+  g_rk_launches.fetch_add(1);
+  return 0;
+}
+
+extern "C" int rk_comm_sharded_step(rk_comm* c, const void* plan_host, const void* plan_dev,
+                                    int optimizer, const void* table_dev,
+                                    const float* total_norm_dev, float max_norm, int max_ctas,
+                                    int use_multicast, void* stream) {
+  if (optimizer == 0)
+    return launch_sharded<AdamOp, AdamTable>(c, plan_host, plan_dev, table_dev, total_norm_dev,
+                                             max_norm, max_ctas, use_multicast, stream);
+  if (optimizer == 1)
+    return launch_sharded<SgdOp, SgdTable>(c, plan_host, plan_dev, table_dev, total_norm_dev,
+                                           max_norm, max_ctas, use_multicast, stream);
+  RK_REQUIRE(false, RK_ERR_INVALID, "rk_comm_sharded_step: optimizer %d (0 = Adam(W), 1 = SGD)",
+             optimizer);
 }
 
 extern "C" int rk_comm_destroy(rk_comm* c) {

@@ -244,18 +244,27 @@ class Engine:
         if isinstance(obj, torch.nn.Module):
             return self._prepare_model(obj)
         if isinstance(obj, torch.optim.Optimizer):
-            opt = EngineOptimizer(obj, self)
-            if self.num_processes > 1:
-                cls = P2PGradSync if opt.arena is not None else GradSync
-                self._grad_sync[id(opt)] = cls(opt, self, self._bucket_cap_mb)
-                self.grad_sync_kinds.append(cls.__name__)
-            self._optimizers.append(opt)
-            return opt
+            return self.prepare_optimizer(obj)
         if isinstance(obj, torch.optim.lr_scheduler.LRScheduler):
             sched = EngineScheduler(obj, self)
             self._schedulers.append(sched)
             return sched
         return obj
+
+    def prepare_optimizer(self, obj: torch.optim.Optimizer, sharded: bool | None = None):
+        """``prepare`` for an optimizer, with the one choice ``prepare`` has no argument for:
+        ``sharded=True`` makes each rank update 1/W of the parameters and write them to all
+        ranks over NVLink (rk_comm_sharded_step) instead of repeating the whole step on every
+        replica.  Same results bit for bit; default from ROCKET_B200_SHARDED_STEP, else off."""
+        if sharded is None:
+            sharded = os.environ.get("ROCKET_B200_SHARDED_STEP", "0") == "1"
+        opt = EngineOptimizer(obj, self, sharded=sharded)
+        if self.num_processes > 1:
+            cls = P2PGradSync if opt.arena is not None else GradSync
+            self._grad_sync[id(opt)] = cls(opt, self, self._bucket_cap_mb)
+            self.grad_sync_kinds.append(cls.__name__ + ("+sharded" if opt.sharded else ""))
+        self._optimizers.append(opt)
+        return opt
 
     def _prepare_model(self, model: torch.nn.Module) -> torch.nn.Module:
         if self.num_processes > 1:
@@ -342,6 +351,9 @@ class Engine:
         if sync is not None:
             return sync.grad_scale
         return 1.0 / self.num_processes if opt is None else 1.0
+
+    def grad_sync_of(self, opt):
+        return self._grad_sync.get(id(opt))
 
     def finish_grad_sync(self, opt) -> bool:
         """Complete the gradient exchange of this step.  True if it also left the norm's

@@ -31,9 +31,13 @@ def _align(n: int) -> int:
 
 
 class EngineOptimizer:
-    def __init__(self, optimizer: torch.optim.Optimizer, engine) -> None:
+    def __init__(self, optimizer: torch.optim.Optimizer, engine, sharded: bool = False) -> None:
         self.optimizer = optimizer
         self.engine = engine
+        # sharded step (csrc/rk_comm.cu, K7): every rank updates 1/W of the chunks and writes
+        # the new parameters to all ranks.  Needs the NVLink exchange path; otherwise the step
+        # stays replicated (which is what one GPU is anyway).
+        self.sharded = bool(sharded) and engine.num_processes > 1 and engine.wants_p2p()
         self.max_grad_norm: float | None = None
         self.last_grad_norm: torch.Tensor | None = None   # device scalar, for logging
         self._zeroed_by_step = False
@@ -83,7 +87,6 @@ class EngineOptimizer:
         if not self._params:
             raise ValueError("optimizer has no trainable parameters")
         self._total = off
-        self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
         # Gradients live in an "arena" when the fused NVLink all-reduce will be used: one
         # allocation [signal pad | norm scratch | gradients] that the peer ranks map (comm.py).
         self.arena = self._scratch_view = None
@@ -93,12 +96,19 @@ class EngineOptimizer:
             scratch = -(-self.engine.backend.scratch_bytes([p.numel() for p in self._params])
                         // 256) * 256
             from rocket_b200.comm import alloc_arena
-            self.arena = alloc_arena(sig + scratch + 4 * off, dev)
+            # sharded step: the parameters follow the gradients, so that owners can write
+            # them into every rank's copy      [signals | scratch | gradients | parameters]
+            self.arena = alloc_arena(sig + scratch + 4 * off * (2 if self.sharded else 1), dev)
             self._scratch_offset = sig
             self._scratch_view = self.arena[sig:sig + scratch]
-            self.flat_g = self.arena[sig + scratch:].view(torch.float32)
+            g0 = sig + scratch
+            self.flat_g = self.arena[g0:g0 + 4 * off].view(torch.float32)
+            if self.sharded:
+                self.flat_p = self.arena[g0 + 4 * off:].view(torch.float32)
         else:
             self.flat_g = torch.zeros(off, dtype=torch.float32, device=dev)
+        if not self.sharded:
+            self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
         self._needs_m = self._kind != "sgd" or any(
             g.get("momentum", 0) != 0 for g in self.optimizer.param_groups)
         self.flat_m = torch.zeros(off, dtype=torch.float32, device=dev) if self._needs_m else None
@@ -119,17 +129,19 @@ class EngineOptimizer:
         self._grad_ptr = [v.data_ptr() for v in self._views_g]
         self._adopted = [False] * len(self._params)      # grad lives in flat_g
         self._group_step = [0] * len(self.optimizer.param_groups)
-        self._import_state()
         self._plan = None
         self._table_ring = None
         self._dev_table = torch.zeros(4096, dtype=torch.uint8, device=dev)
+        self._import_state()
 
     def _import_state(self) -> None:
         """Adopt state the wrapped optimizer already holds (resume / prior training)."""
+        found = False
         for i, p in enumerate(self._params):
             st = self.optimizer.state.get(p)
             if not st:
                 continue
+            found = True
             gi = self._group_of[i]
             if "step" in st:
                 self._group_step[gi] = max(self._group_step[gi], int(float(st["step"])))
@@ -144,6 +156,37 @@ class EngineOptimizer:
                     self._views_m[i].copy_(st["exp_avg"])
                     self._views_v[i].copy_(st["exp_avg_sq"])
                     st["exp_avg"], st["exp_avg_sq"] = self._views_m[i], self._views_v[i]
+        if self.sharded and found:
+            for flat in (self.flat_m, self.flat_v):
+                if flat is not None:
+                    self._zero_unowned(flat)
+
+    # ---- sharded step: who owns what ---------------------------------------------------------
+    def _zero_unowned(self, flat: torch.Tensor) -> None:
+        """Keep only this rank's chunks of a moment buffer (norm chunk c belongs to rank
+        c % W, as in the exchange kernel); the rest is held at zero, which is what lets
+        ``_gathered`` rebuild the full buffer with one integer SUM."""
+        plan = self._get_plan()
+        world, rank = self.engine.num_processes, self.engine.process_index
+        chunk, prefix = plan.chunk_norm, plan.prefix_norm
+        for i, (p, o) in enumerate(zip(self._params, self._offsets)):
+            n, c0 = p.numel(), int(prefix[i])
+            full = n // chunk
+            if full:
+                rows = flat[o:o + full * chunk].view(full, chunk)
+                for k in range(world):
+                    if k != rank:
+                        rows[(k - c0) % world::world].zero_()
+            if n % chunk and (c0 + full) % world != rank:
+                flat[o + full * chunk:o + n].zero_()
+
+    def _gathered(self, flat: torch.Tensor) -> torch.Tensor:
+        """Collective: the full moment buffer, bit for bit (every element is non-zero on at
+        most one rank, so summing the bit patterns as integers reproduces the owner's)."""
+        import torch.distributed as dist
+        full = flat.clone()
+        dist.all_reduce(full.view(torch.int32), op=dist.ReduceOp.SUM)
+        return full
 
     # ---- the AcceleratedOptimizer surface ---------------------------------------------------
     @property
@@ -215,13 +258,26 @@ class EngineOptimizer:
                 self.last_grad_norm = norm
         self._pending_clip = None
         groups = self._step_groups()
-        if gp is None:
+        if self.sharded:
+            if gp is not None:
+                raise NotImplementedError("Module(graph=True) with a sharded optimizer step")
+            slot, uploaded = self._table_slot()
+            eng.backend.step_table_write(self._kind, groups, slot)
+            self._dev_table.copy_(slot, non_blocking=True)
+            uploaded.record()
+            sync = eng.grad_sync_of(self)
+            eng.backend.comm_sharded_step(
+                sync._comm, plan, self._kind, self._dev_table.data_ptr(), norm,
+                float(max_norm) if max_norm is not None else 0.0, sync.step_ctas,
+                sync.use_multicast)
+        elif gp is None:
             fn = eng.backend.sgd_step if self._kind == "sgd" else eng.backend.adam_step
             fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)
         else:
             # Kernel arguments are frozen inside a graph: this step's constants go through a
             # pinned ring slot into a device table, uploaded in stream order before the replay.
-            slot = self._table_slot()
+            slot, uploaded = self._table_slot()
+            gp.post.append(uploaded.record)
             eng.backend.step_table_write(self._kind, groups, slot)
             table = self._dev_table
             gp.pre.append(lambda: table.copy_(slot, non_blocking=True))
@@ -259,10 +315,11 @@ class EngineOptimizer:
 
     _TABLE_SLOTS = 32
 
-    def _table_slot(self) -> torch.Tensor:
-        """Next slot of the pinned ring the step tables are staged in.  A slot is reused only
-        after the upload that read it has executed, which also bounds how far the host can
-        run ahead of the device."""
+    def _table_slot(self):
+        """Next slot of the pinned ring the step tables are staged in, and the event the
+        caller records once the slot's upload has been issued.  A slot is reused only after
+        that upload has executed, which also bounds how far the host can run ahead of the
+        device."""
         from rocket_b200 import _native as N
         if self._table_ring is None:
             self._table_ring = torch.zeros(self._TABLE_SLOTS, N.RK_STEP_TABLE_BYTES,
@@ -275,8 +332,7 @@ class EngineOptimizer:
             self._table_events[i].synchronize()
         ev = torch.cuda.Event()
         self._table_events[i] = ev
-        self.engine.graph_pass.post.append(ev.record)
-        return self._table_ring[i]
+        return self._table_ring[i], ev
 
     # ---- gradient adoption -----------------------------------------------------------------------
     def _adopt_grads(self) -> None:
@@ -321,6 +377,15 @@ class EngineOptimizer:
 
     # ---- state in torch's own format (checkpoints) ----------------------------------------------------
     def _export_state(self) -> None:
+        views_m, views_v = self._views_m, self._views_v
+        if self.sharded:     # collective: every rank has to get here
+            def views(flat):
+                if flat is None:
+                    return [None] * len(self._params)
+                full = self._gathered(flat)
+                return [full[o:o + p.numel()].view(p.shape)
+                        for p, o in zip(self._params, self._offsets)]
+            views_m, views_v = views(self.flat_m), views(self.flat_v)
         for i, p in enumerate(self._params):
             if not self._adopted[i]:
                 continue
@@ -329,10 +394,10 @@ class EngineOptimizer:
                 continue
             st = self.optimizer.state[p]
             if self._kind == "sgd":
-                st["momentum_buffer"] = self._views_m[i] if self._needs_m else None
+                st["momentum_buffer"] = views_m[i] if self._needs_m else None
             else:
                 st["step"] = torch.tensor(float(step), dtype=torch.float32)
-                st["exp_avg"], st["exp_avg_sq"] = self._views_m[i], self._views_v[i]
+                st["exp_avg"], st["exp_avg_sq"] = views_m[i], views_v[i]
 
     def state_dict(self) -> dict:
         self._export_state()

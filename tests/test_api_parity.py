@@ -18,7 +18,8 @@ import oracle
 FROZEN = json.loads((Path(__file__).parent / "golden" / "api_signatures.json").read_text())
 CLASSES = [c for c in FROZEN if c not in ("Events", "utils.torch", "utils.collections")]
 # the single additive keyword: default None = reference behaviour
-ADDITIVE = {("Optimizer", "__init__"): ["max_grad_norm"], ("Module", "__init__"): ["graph"]}
+ADDITIVE = {("Optimizer", "__init__"): ["max_grad_norm", "sharded"],
+            ("Module", "__init__"): ["graph"]}
 
 
 def _sig(fn):

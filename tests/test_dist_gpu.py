@@ -25,10 +25,10 @@ GOLDEN = Path(__file__).parent / "golden"
 
 
 def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str,
-                sync: str = "p2p", graph: bool = False) -> None:
+                sync: str = "p2p", graph: bool = False, sharded: bool = False) -> None:
     os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
                       MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), TQDM_DISABLE="1",
-                      ROCKET_B200_GRAD_SYNC=sync)
+                      ROCKET_B200_GRAD_SYNC=sync, ROCKET_B200_SHARDED_STEP=str(int(sharded)))
     root = Path(__file__).resolve().parent.parent
     for p in (str(root), str(root / "tests")):
         if p not in sys.path:
@@ -52,10 +52,17 @@ def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str,
         assert launcher._capsules[0]._capsules[1].graphs_captured >= 1, "no step was captured"
         sync = "p2p_graph"
     # the path under test really ran (no silent fall back to the other exchange)
-    assert engines[0].grad_sync_kinds == ["GradSync" if sync == "nccl" else "P2PGradSync"], \
-        engines[0].grad_sync_kinds
-    np.savez_compressed(Path(out_dir) / f"{case}_{sync}_rank{rank}.npz",
-                        **dist_worker._collect(h, tracker))
+    want = "GradSync" if sync == "nccl" else "P2PGradSync" + ("+sharded" if sharded else "")
+    assert engines[0].grad_sync_kinds == [want], engines[0].grad_sync_kinds
+    out = dist_worker._collect(h, tracker)
+    # optimizer state as torch.optim holds it after the run (Optimizer.destroy exported it)
+    for i, p in enumerate(h["net"].parameters()):
+        for name, t in h["opt"].state.get(p, {}).items():
+            if torch.is_tensor(t):
+                out[f"state/{i}/{name}"] = t.detach().cpu().numpy().copy()
+    if sharded:
+        sync = "p2p_sharded"
+    np.savez_compressed(Path(out_dir) / f"{case}_{sync}_rank{rank}.npz", **out)
     import torch.distributed as dist
     if dist.is_initialized():
         dist.destroy_process_group()
@@ -115,6 +122,35 @@ def test_graph_captured_step_with_nvlink_exchange_equals_eager(tmp_path):
             assert np.array_equal(b[k].view(np.int32), c[k].view(np.int32)), k
     assert a["loss_values"].tolist() == b["loss_values"].tolist()
     assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("case", list(dist_worker.WS2_CASES))
+def test_sharded_optimizer_step_equals_replicated_bitwise(case, tmp_path):
+    """Sharded step (reduce-scatter + owner update + parameter write to all ranks over NVLink)
+    against the replicated step after the fused all-reduce: per element the arithmetic is the
+    same, so parameters, losses, counts AND the optimizer state torch.optim ends up holding
+    (moments gathered from their owners) must agree bit for bit, on both ranks."""
+    port = 29870 + 2 * list(dist_worker.WS2_CASES).index(case)
+    mp.spawn(_gpu_worker, args=(2, port, case, str(tmp_path), "p2p", False, False),
+             nprocs=2, join=True)
+    mp.spawn(_gpu_worker, args=(2, port + 1, case, str(tmp_path), "p2p", False, True),
+             nprocs=2, join=True)
+    a = np.load(tmp_path / f"{case}_p2p_rank0.npz")
+    n_state = 0
+    for r in range(2):
+        b = np.load(tmp_path / f"{case}_p2p_sharded_rank{r}.npz")
+        assert sorted(a.files) == sorted(b.files)
+        for k in a.files:
+            if k.startswith(("param/", "state/")):
+                assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), (r, k)
+                n_state += k.startswith("state/")
+        if r == 0:                                    # trackers log on the main process only
+            assert len(b["loss_values"]) > 0
+            assert a["loss_values"].tolist() == b["loss_values"].tolist()
+        assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
+    if case == "ws2_adamw_clip":
+        assert n_state > 0
 
 
 def _allreduce_worker(rank: int, world: int, port: int, out_dir: str, arena_kind: str,
@@ -207,6 +243,137 @@ def test_fused_allreduce_norm_kernel_against_nccl(world, path, tmp_path):
     kind, mode = path.split("-")
     port = 29870 + world * 3 + ["ipc-p2p", "symm-p2p", "symm-multicast"].index(path)
     mp.spawn(_allreduce_worker, args=(world, port, str(tmp_path), kind, mode == "multicast"),
+             nprocs=world, join=True)
+    if (tmp_path / "skipped_0").exists():
+        pytest.skip("this box has no NVSwitch multicast support")
+
+
+def _sharded_step_worker(rank: int, world: int, port: int, out_dir: str, multicast: bool,
+                         kind: str) -> None:
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    root = Path(__file__).resolve().parent.parent
+    sys.path.insert(0, str(root))
+    import torch.distributed as dist
+    from rocket_b200 import _native as N
+    from rocket_b200.backend import NativeBackend, TensorSpec
+    from rocket_b200.comm import alloc_arena, map_arena
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    be = NativeBackend(dev)
+    sizes = [6, 10, 150, 4097, 48000, 1, 0, 123457, 3_000_001]
+    groups_of = [0, 1, 0, 1, 0, 1, 0, 1, 0]
+    offs, total = [], 0
+    for n in sizes:
+        offs.append(total)
+        total += (n + 63) // 64 * 64
+    sig = N.RK_COMM_SIGNAL_BYTES
+    scratch = -(-be.scratch_bytes(sizes) // 256) * 256
+    arena = alloc_arena(sig + scratch + 8 * total, dev)      # [signals|scratch|g|p]
+    flat_g = arena[sig + scratch:sig + scratch + 4 * total].view(torch.float32)
+    flat_p = arena[sig + scratch + 4 * total:].view(torch.float32)
+    sgd = kind == "sgd"
+    flat_m = torch.zeros(total, device=dev)
+    flat_v = None if sgd else torch.zeros(total, device=dev)
+    ref_p, ref_g, ref_m = (torch.zeros(total, device=dev) for _ in range(3))
+    ref_v = None if sgd else torch.zeros(total, device=dev)
+
+    def specs_of(p, g, m, v):
+        return [TensorSpec(p=p[o:o + n], g=g[o:o + n], m=m[o:o + n],
+                           v=None if v is None else v[o:o + n], group=gi)
+                for o, n, gi in zip(offs, sizes, groups_of)]
+    plan = be.make_plan(specs_of(flat_p, flat_g, flat_m, flat_v), scratch=arena[sig:sig + scratch])
+    ref_plan = be.make_plan(specs_of(ref_p, ref_g, ref_m, ref_v))
+
+    class Eng:
+        device, process_index, num_processes = dev, rank, world
+    ptrs, mc_ptr, peers = map_arena(arena, Eng)
+    if multicast and not mc_ptr:
+        dist.barrier()
+        dist.destroy_process_group()
+        Path(out_dir, f"skipped_{rank}").write_text("no multicast support")
+        return
+    comm = be.comm_create(rank, world, ptrs, sig, mc_ptr)
+    torch.manual_seed(7)
+    for o, n in zip(offs, sizes):
+        flat_p[o:o + n].normal_(0, 0.1)
+    ref_p.copy_(flat_p)
+    table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8, device=dev)
+    host_table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8).pin_memory()
+    dist.barrier()
+    stream = torch.cuda.current_stream().cuda_stream
+    half = plan.n_chunks_norm // 2
+    owner = torch.zeros(total, dtype=torch.bool, device=dev)       # elements this rank owns
+    for i, (o, n) in enumerate(zip(offs, sizes)):
+        c = torch.arange(n, device=dev) // plan.chunk_norm + int(plan.prefix_norm[i])
+        owner[o:o + n] = (c % world) == rank
+    for it in range(3):
+        torch.manual_seed(100 * it + rank)
+        flat_g.zero_()
+        for o, n in zip(offs, sizes):
+            flat_g[o:o + n].normal_(0, 1e-2)
+        if it == 1:
+            flat_g[offs[4]:offs[4] + 4000].zero_()        # zero gradients: the special values
+        mine = flat_g.clone()
+        if sgd:
+            groups = [dict(lr=0.05, momentum=0.9, dampening=0.0, weight_decay=1e-4,
+                           nesterov=gi == 1, first_step=it == 0, skip=False) for gi in range(2)]
+        else:
+            groups = [dict(lr=1e-3 * (gi + 1), beta1=0.9, beta2=0.999, eps=1e-8,
+                           weight_decay=0.01 * gi, step=it + 1, decoupled=True, skip=False)
+                      for gi in range(2)]
+        max_norm = 0.0 if it == 2 else 0.05
+        # replicated arm: fused all-reduce, then the ordinary step kernel on private copies
+        torch.cuda.synchronize(); dist.barrier()
+        be.comm_allreduce_norm(comm, plan, half, plan.n_chunks_norm, 0, 0, stream, multicast)
+        be.comm_allreduce_norm(comm, plan, 0, half, 1, 0, stream, multicast)
+        norm_a = be.l2norm_finalize(plan).clone()
+        ref_g.copy_(flat_g)
+        (be.sgd_step if sgd else be.adam_step)(ref_plan, groups, norm_a if max_norm else None,
+                                               max_norm, 1.0, True)
+        torch.cuda.synchronize(); dist.barrier()
+        # sharded arm on the same inputs
+        flat_g.copy_(mine)
+        torch.cuda.synchronize(); dist.barrier()
+        be.comm_reduce_scatter_norm(comm, plan, half, plan.n_chunks_norm, 0, 0, stream, multicast)
+        be.comm_reduce_scatter_norm(comm, plan, 0, half, 1, 0, stream, multicast)
+        norm_b = be.l2norm_finalize(plan)
+        be.step_table_write(kind, groups, host_table)
+        table.copy_(host_table, non_blocking=True)
+        be.comm_sharded_step(comm, plan, kind, table.data_ptr(), norm_b if max_norm else None,
+                             max_norm, 0, multicast)
+        torch.cuda.synchronize()
+        assert torch.equal(norm_a, norm_b), (it, float(norm_a), float(norm_b))
+        assert torch.equal(flat_p.view(torch.int32), ref_p.view(torch.int32)), \
+            (it, int((flat_p != ref_p).sum()))
+        assert not flat_g.any(), it
+        pairs = [(flat_m, ref_m)] + ([] if sgd else [(flat_v, ref_v)])
+        for mine_s, ref_s in pairs:
+            assert torch.equal(mine_s[owner].view(torch.int32), ref_s[owner].view(torch.int32)), it
+            assert not mine_s[~owner].any(), it           # other ranks' chunks are never touched
+            full = mine_s.clone()
+            dist.all_reduce(full.view(torch.int32))
+            assert torch.equal(full.view(torch.int32), ref_s.view(torch.int32)), it
+    dist.barrier()
+    be.comm_destroy(comm)
+    del peers
+    torch.cuda.ipc_collect()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("kind", ["adamw", "sgd"])
+@pytest.mark.parametrize("path", ["p2p", "multicast"])
+def test_sharded_step_kernel_against_replicated_step(world, kind, path, tmp_path):
+    """rk_comm_reduce_scatter_norm + rk_comm_sharded_step on awkward sizes against
+    rk_comm_allreduce_norm + the ordinary step kernel: same norm, same parameters on every
+    rank, moments equal on their owners and untouched elsewhere, gradients zero-filled."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    port = 29930 + world * 4 + 2 * (kind == "sgd") + (path == "multicast")
+    mp.spawn(_sharded_step_worker, args=(world, port, str(tmp_path), path == "multicast", kind),
              nprocs=world, join=True)
     if (tmp_path / "skipped_0").exists():
         pytest.skip("this box has no NVSwitch multicast support")
