@@ -548,6 +548,7 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
             ts.append(e[1].elapsed_time(e[2]))
     # the same step with the optimizer sharded: reduce-scatter (+ norm), then every rank
     # updates the 1/W of the chunks it owns and writes the new parameters to all ranks
+    # (P2P loads / stores at every W, like the engine: comm.P2PGradSync)
     table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8, device=dev)
     host_table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8).pin_memory()
     m.zero_()
@@ -562,11 +563,10 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
         dist.barrier()
         e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
         e[0].record()
-        be.comm_reduce_scatter_norm(comm, plan, 0, plan.n_chunks_norm, 0, 74 if use_mc else 0,
-                                    stream, use_mc)
+        be.comm_reduce_scatter_norm(comm, plan, 0, plan.n_chunks_norm, 0, 0, stream, False)
         norm = be.l2norm_finalize(plan)
         e[1].record()
-        be.comm_sharded_step(comm, plan, "adamw", table.data_ptr(), norm, 1.0, 0, use_mc)
+        be.comm_sharded_step(comm, plan, "adamw", table.data_ptr(), norm, 1.0, 0, False)
         e[2].record()
         torch.cuda.synchronize()
         if i >= warmup:

@@ -160,8 +160,11 @@ class P2PGradSync(_BucketedSync):
         ptrs, self.multicast_ptr, self._peers = map_arena(opt.arena, engine)
         # in-switch reduction moves ~G bytes per GPU instead of 2(W-1)/W * G: a win from W = 4
         want_mc = os.environ.get("ROCKET_B200_MULTICAST", "auto")
+        # (the sharded step's two kernels each move (W-1)/W of the data in ONE direction, which
+        # the switch cannot shrink: P2P measured faster there, 4 GPUs: 4.74 vs 5.73 ms per 5e8)
         self.use_multicast = bool(self.multicast_ptr) and (
-            want_mc == "1" or (want_mc == "auto" and engine.num_processes >= 4))
+            want_mc == "1" or (want_mc == "auto" and engine.num_processes >= 4
+                               and not opt.sharded))
         if self.use_multicast and self.max_ctas == 0:
             self.max_ctas = 74      # the switch does the work: half the SMs issue enough
         self.step_ctas = int(os.environ.get("ROCKET_B200_SHARDED_STEP_CTAS", "0"))

@@ -319,7 +319,9 @@ static int launch_exchange(rk_comm* c, const void* plan_host, const void* plan_d
              h->n_chunks_norm);
   const int W = c->world;
   const int owned = (chunk_hi - chunk_lo + W - 1) / W;
-  int grid = max_ctas > 0 ? max_ctas : c->sms;
+  // reduce-scatter keeps its stores local and is limited by loads in flight: two CTAs per SM
+  // (1e9 params, 2 GPUs: 4.09 -> 3.27 ms; all-reduce does not gain)
+  int grid = max_ctas > 0 ? max_ctas : (broadcast ? c->sms : 2 * c->sms);
   if (grid > owned) grid = owned;
   if (grid < 1) grid = 1;   // still takes part in both barriers
   const float scale = 1.0f / (float)W;
@@ -387,7 +389,14 @@ rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
   pr.coef = pr.has_clip ? rk_clip_coef(__ldg(total_norm), max_norm) : 1.0f;
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
 
-  for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+  // A CTA takes whole rows of W consecutive chunks: one it owns (heavy: update + W-way store)
+  // and W-1 it only zero-fills.  Striding single chunks by gridDim would hand all the owned
+  // chunks to 1/W of the CTAs whenever gridDim is a multiple of W.
+  const int rows = (n_chunks + W - 1) / W;
+  for (int k = blockIdx.x; k < rows; k += gridDim.x)
+  for (int q = 0; q < W; ++q) {
+    const int c = k * W + q;
+    if (c >= n_chunks) break;
     const int t = rk_find_tensor(prefix, n_tensors, c);
     const rk_tensor_desc d = descs[t];
     Op op;
@@ -399,7 +408,7 @@ rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
     float* P = d.p + base;
     float* G = d.g + base;
     const bool vec = (d.flags & RK_TENSOR_VEC4) != 0;
-    if (c % W != rank) {                     // not mine: only clear my local gradient
+    if (q != rank) {                         // not mine: only clear my local gradient
       if (vec) {
         const int nvec = count >> 2;
         for (int i = tid; i < nvec; i += COMM_THREADS) stg4<0>(G + 4 * i, zero4);
@@ -489,7 +498,8 @@ static int launch_sharded(rk_comm* c, const void* plan_host, const void* plan_de
   const rk_plan_header* h = (const rk_plan_header*)plan_host;
   RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "rk_comm_sharded_step: bad plan magic");
   int grid = max_ctas > 0 ? max_ctas : 3 * c->sms;
-  if (grid > h->n_chunks_norm) grid = h->n_chunks_norm;
+  const int rows = (h->n_chunks_norm + c->world - 1) / c->world;
+  if (grid > rows) grid = rows;
   if (grid < 1) grid = 1;
   const int bucket = RK_COMM_MAX_BUCKETS - 1;   // this kernel's own barrier slot
   const bool mc = c->mc_arena != nullptr && use_multicast != 0;

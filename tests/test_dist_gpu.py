@@ -124,21 +124,24 @@ def test_graph_captured_step_with_nvlink_exchange_equals_eager(tmp_path):
     assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("world", [2, 4])
 @pytest.mark.parametrize("case", list(dist_worker.WS2_CASES))
-def test_sharded_optimizer_step_equals_replicated_bitwise(case, tmp_path):
+def test_sharded_optimizer_step_equals_replicated_bitwise(case, world, tmp_path):
     """Sharded step (reduce-scatter + owner update + parameter write to all ranks over NVLink)
     against the replicated step after the fused all-reduce: per element the arithmetic is the
     same, so parameters, losses, counts AND the optimizer state torch.optim ends up holding
-    (moments gathered from their owners) must agree bit for bit, on both ranks."""
+    (moments gathered from their owners) must agree bit for bit, on every rank.  Four ranks
+    take the NVSwitch multicast variants of both kernels."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     port = 29870 + 2 * list(dist_worker.WS2_CASES).index(case)
-    mp.spawn(_gpu_worker, args=(2, port, case, str(tmp_path), "p2p", False, False),
-             nprocs=2, join=True)
-    mp.spawn(_gpu_worker, args=(2, port + 1, case, str(tmp_path), "p2p", False, True),
-             nprocs=2, join=True)
+    mp.spawn(_gpu_worker, args=(world, port, case, str(tmp_path), "p2p", False, False),
+             nprocs=world, join=True)
+    mp.spawn(_gpu_worker, args=(world, port + 1, case, str(tmp_path), "p2p", False, True),
+             nprocs=world, join=True)
     a = np.load(tmp_path / f"{case}_p2p_rank0.npz")
     n_state = 0
-    for r in range(2):
+    for r in range(world):
         b = np.load(tmp_path / f"{case}_p2p_sharded_rank{r}.npz")
         assert sorted(a.files) == sorted(b.files)
         for k in a.files:
