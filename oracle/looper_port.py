@@ -98,7 +98,7 @@ class OracleOptimizer:
 
 def train_epoch(net, objective, opt, sched, batches, *, accum: int, max_norm, device,
                 state: dict, world: int = 1, sync_loss: bool = True,
-                autocast_dtype=None) -> None:
+                autocast_dtype=None, scaler=None) -> None:
     """One pass over ``batches`` (a sized iterable of CPU batches). Appends to ``state``:
     loss_steps/loss_values, lr_steps/lr_values; keeps the cross-epoch counters there."""
     net.train()
@@ -129,16 +129,30 @@ def train_epoch(net, objective, opt, sched, batches, *, accum: int, max_norm, de
                 state["loss_values"].append(value)
                 state["loss_step"] += 1
                 value = 0.0
-            (loss / accum).backward()
+            # accelerate.backward: scaler.scale(loss / accum).backward() under fp16
+            scaled = loss / accum
+            (scaler.scale(scaled) if scaler is not None else scaled).backward()
         if sync:
+            skipped = False
+            if scaler is not None:
+                # accelerate: clip_grad_norm_ unscales first; optimizer.step goes through
+                # scaler.step (skipped on overflow) + scaler.update; an overflowing step also
+                # skips the scheduler (AcceleratedScheduler checks step_was_skipped)
+                before = scaler.get_scale()
+                scaler.unscale_(opt)
             if max_norm is not None and not isinstance(opt, OracleOptimizer):
                 torch.nn.utils.clip_grad_norm_(net.parameters(), max_norm, foreach=False)
-            opt.step()
+            if scaler is not None:
+                scaler.step(opt)
+                scaler.update()
+                skipped = scaler.get_scale() < before
+            else:
+                opt.step()
             opt.zero_grad()
             state["lr_steps"].append(state["opt_step"])
             state["lr_values"].append(opt.param_groups[0]["lr"])
             state["opt_step"] += 1
-            if sched is not None:
+            if sched is not None and not skipped:
                 for _ in range(world):
                     sched.step()
         elif sched is not None:
@@ -147,12 +161,15 @@ def train_epoch(net, objective, opt, sched, batches, *, accum: int, max_norm, de
 
 
 @torch.no_grad()
-def eval_epoch(net, batches, *, device) -> tuple[int, int]:
+def eval_epoch(net, batches, *, device, autocast_dtype=None) -> tuple[int, int]:
     net.eval()
     positive = total = 0
     for batch in batches:
         batch = [t.to(device) if isinstance(t, torch.Tensor) else t for t in batch]
-        _, gt, logits = net(batch)
+        amp = torch.autocast(device_type=torch.device(device).type, dtype=autocast_dtype) \
+            if autocast_dtype is not None else contextlib.nullcontext()
+        with amp:
+            _, gt, logits = net(batch)
         pr = logits.argmax(1)
         total += pr.numel()
         positive += int(torch.sum(gt == pr))
@@ -166,7 +183,8 @@ def new_state() -> dict:
 
 def run_mnist_port(*, device="cpu", seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_size=64,
                    optimizer="adamw", max_norm=None, accum=2, epochs=2, sched_step=5, lr=1e-3,
-                   net=None, workloads=None, optimizer_impl="torch") -> dict:
+                   net=None, workloads=None, optimizer_impl="torch", mixed_precision=None,
+                   input_scale=1.0) -> dict:
     """The graph of tests/workloads.build_mnist_graph, as straight-line code."""
     if workloads is None:
         import workloads  # tests/workloads.py (on sys.path in tests and bench)
@@ -185,8 +203,11 @@ def run_mnist_port(*, device="cpu", seed=0, n_train=64 * 24, n_val=64 * 5 + 13, 
     if optimizer_impl == "oracle":
         opt._opt_called = True                      # keep LRScheduler's order check quiet
         opt = OracleOptimizer(opt, max_norm)
-    train = workloads.synthetic_classification(n_train, (1, 28, 28), 10, seed + 1)
-    val = workloads.synthetic_classification(n_val, (1, 28, 28), 10, seed + 2)
+    train = workloads.synthetic_classification(n_train, (1, 28, 28), 10, seed + 1, input_scale)
+    val = workloads.synthetic_classification(n_val, (1, 28, 28), 10, seed + 2, input_scale)
+    amp_dtype = {None: None, "bf16": torch.bfloat16, "fp16": torch.float16}[mixed_precision]
+    scaler = torch.amp.GradScaler(torch.device(device).type) if mixed_precision == "fp16" \
+        else None
     net.to(device)
     objective = workloads.CrossEntropy()
     tl = torch.utils.data.DataLoader(train, batch_size=batch_size, shuffle=False)
@@ -194,14 +215,14 @@ def run_mnist_port(*, device="cpu", seed=0, n_train=64 * 24, n_val=64 * 5 + 13, 
     state = new_state()
     for epoch in range(epochs):
         train_epoch(net, objective, opt, sched, tl, accum=accum, max_norm=max_norm,
-                    device=device, state=state)
-        pos, tot = eval_epoch(net, vl, device=device)
+                    device=device, state=state, autocast_dtype=amp_dtype, scaler=scaler)
+        pos, tot = eval_epoch(net, vl, device=device, autocast_dtype=amp_dtype)
         state["accuracy_history"].append((epoch, pos, tot))
         # eval iterations advance accelerate's accumulation phase too (module.py:138,211);
         # the last eval batch resets it
         state["phase"] = 0
     state["params"] = {k: p.detach().cpu().clone() for k, p in net.named_parameters()}
-    state["net"], state["opt"] = net, opt
+    state["net"], state["opt"], state["scaler"] = net, opt, scaler
     return state
 
 

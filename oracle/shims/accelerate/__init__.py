@@ -177,11 +177,12 @@ class DataLoaderShard:
 
 
 class AcceleratedOptimizer:
-    """accelerate.optimizer.AcceleratedOptimizer without scaler / XLA paths."""
+    """accelerate.optimizer.AcceleratedOptimizer without the XLA paths."""
 
-    def __init__(self, optimizer, gradient_state):
+    def __init__(self, optimizer, gradient_state, scaler=None):
         self.optimizer = optimizer
         self.gradient_state = gradient_state
+        self.scaler = scaler
         self._is_overflow = False
 
     @property
@@ -204,8 +205,26 @@ class AcceleratedOptimizer:
                 self.optimizer.zero_grad(set_to_none=set_to_none)
 
     def step(self, closure=None):
-        if self.gradient_state.sync_gradients:
+        if not self.gradient_state.sync_gradients:
+            return
+        if self.scaler is None:
             self.optimizer.step(closure)
+            return
+        # fp16: scaler.step skips optimizer.step on overflow; accelerate learns that by
+        # patching the step method and looking whether it was called
+        called = []
+        original = self.optimizer.step
+
+        def patched(*a, **k):
+            called.append(True)
+            return original(*a, **k)
+        self.optimizer.step = patched
+        try:
+            self.scaler.step(self.optimizer, closure)
+            self.scaler.update()
+        finally:
+            del self.optimizer.step
+        self._is_overflow = not called
 
     def state_dict(self):
         return self.optimizer.state_dict()
@@ -276,6 +295,10 @@ class Accelerator:
         self.device_placement = device_placement
         self.mixed_precision = mixed_precision if mixed_precision not in (None, "no") else "no"
         self.gradient_state = GradientState(gradient_accumulation_steps)
+        # real accelerate refuses fp16 without an accelerator device; the shim lets torch's own
+        # GradScaler run on the CPU so that the unmodified reference can produce fp16 goldens
+        self.scaler = torch.amp.GradScaler(self.device.type) \
+            if self.mixed_precision == "fp16" else None
         self.project_dir = project_dir if project_dir is not None else \
             getattr(project_config, "project_dir", None)
         self.step = 0
@@ -331,7 +354,7 @@ class Accelerator:
             self._models.append(model)
             return model
         if isinstance(obj, torch.optim.Optimizer):
-            opt = AcceleratedOptimizer(obj, self.gradient_state)
+            opt = AcceleratedOptimizer(obj, self.gradient_state, self.scaler)
             self._optimizers.append(opt)
             return opt
         if isinstance(obj, torch.optim.lr_scheduler.LRScheduler):
@@ -374,9 +397,14 @@ class Accelerator:
 
     def backward(self, loss, **kwargs):
         loss = loss / self.gradient_accumulation_steps
+        if self.scaler is not None:
+            loss = self.scaler.scale(loss)
         loss.backward(**kwargs)
 
     def clip_grad_norm_(self, parameters, max_norm, norm_type=2):
+        if self.scaler is not None:          # accelerate: unscale_gradients() first
+            for opt in self._optimizers:
+                self.scaler.unscale_(opt.optimizer)
         return torch.nn.utils.clip_grad_norm_(parameters, max_norm, norm_type=norm_type)
 
     # -- collectives ----------------------------------------------------------------------------
@@ -408,6 +436,8 @@ class Accelerator:
         for i, c in enumerate(self._custom_objects):
             with open(os.path.join(output_dir, f"custom_checkpoint_{i}.pkl"), "wb") as f:
                 pickle.dump(c.state_dict(), f)
+        if self.scaler is not None:
+            torch.save(self.scaler.state_dict(), os.path.join(output_dir, "scaler.pt"))
         torch.save({"torch": torch.get_rng_state()},
                    os.path.join(output_dir, f"random_states_{self.process_index}.pkl"))
         return output_dir
@@ -422,6 +452,8 @@ class Accelerator:
         for i, c in enumerate(self._custom_objects):
             with open(os.path.join(input_dir, f"custom_checkpoint_{i}.pkl"), "rb") as f:
                 c.load_state_dict(pickle.load(f))
+        if self.scaler is not None:
+            self.scaler.load_state_dict(torch.load(os.path.join(input_dir, "scaler.pt")))
 
     # -- trackers --------------------------------------------------------------------------------
     def get_tracker(self, name, unwrap=False):

@@ -29,6 +29,7 @@ from rocket_b200.comm import (BufferSync, GradSync, P2PGradSync, broadcast_modul
                               p2p_possible)
 from rocket_b200.deferred import DeferredScalar
 from rocket_b200.flat import EngineOptimizer
+from rocket_b200.scaler import LossScaler
 from rocket_b200.staging import EngineDataLoader, PinnedRingStager
 
 
@@ -191,11 +192,10 @@ class Engine:
         self.backend = backend
         self.device_placement = device_placement
         self.mixed_precision = mixed_precision if mixed_precision not in (None, "no") else "no"
-        if self.mixed_precision == "fp16":
-            raise NotImplementedError("mixed_precision='fp16' (GradScaler) is not implemented; "
-                                      "use 'bf16'")
-        if self.mixed_precision not in ("no", "bf16"):
+        if self.mixed_precision not in ("no", "bf16", "fp16"):
             raise ValueError(f"unknown mixed_precision {mixed_precision!r}")
+        # fp16: dynamic loss scaling, GradScaler's defaults as accelerate constructs it
+        self.scaler = LossScaler(self.device) if self.mixed_precision == "fp16" else None
         self._accum_steps = int(gradient_accumulation_steps)
         self.sync_gradients = True
         self.step = 0
@@ -271,12 +271,13 @@ class Engine:
             broadcast_module_state(model, src=0)
             if any(True for _ in model.buffers()):
                 self._buffer_sync.append(BufferSync(model))
-        if self.mixed_precision == "bf16" and not getattr(model, "_rk_autocast", False):
+        if self.mixed_precision in ("bf16", "fp16") and not getattr(model, "_rk_autocast", False):
             inner = model.forward
             dev_type = self.device.type
+            dtype = self._autocast_dtype
 
             def forward(*args, **kwargs):
-                with torch.autocast(device_type=dev_type, dtype=torch.bfloat16):
+                with torch.autocast(device_type=dev_type, dtype=dtype):
                     out = inner(*args, **kwargs)
                 return _to_fp32(out)
 
@@ -320,18 +321,25 @@ class Engine:
 
     @contextlib.contextmanager
     def autocast(self, autocast_handler=None):
-        if self.mixed_precision == "bf16":
-            with torch.autocast(device_type=self.device.type, dtype=torch.bfloat16):
+        if self.mixed_precision in ("bf16", "fp16"):
+            with torch.autocast(device_type=self.device.type, dtype=self._autocast_dtype):
                 yield
         else:
             yield
+
+    @property
+    def _autocast_dtype(self):
+        return torch.bfloat16 if self.mixed_precision == "bf16" else torch.float16
 
     def backward(self, loss: torch.Tensor, **kwargs) -> None:
         """reference loss.py:119: scale by 1/accumulation_steps, then autograd.  Bucketed
         all-reduces start from gradient hooks while this runs (sync steps only)."""
         if self.graph_pass is not None and self.graph_pass.mode == "replay":
             return                                   # backward is part of the graph
-        (loss / self._accum_steps).backward(**kwargs)
+        loss = loss / self._accum_steps
+        if self.scaler is not None:                  # accelerate: scaler.scale(loss).backward()
+            loss = self.scaler.scale(loss)
+        loss.backward(**kwargs)
 
     # ---- gradient exchange -----------------------------------------------------------------------------
     def wants_p2p(self) -> bool:
@@ -480,6 +488,8 @@ class Engine:
             for i, sd in enumerate(states["custom"]):
                 with open(os.path.join(output_dir, f"custom_checkpoint_{i}.pkl"), "wb") as f:
                     pickle.dump(sd, f)
+            if self.scaler is not None:          # accelerate: scaler.pt, GradScaler's format
+                torch.save(self.scaler.state_dict(), os.path.join(output_dir, "scaler.pt"))
         os.makedirs(output_dir, exist_ok=True)
         rng = {"torch": torch.get_rng_state()}
         if self.device.type == "cuda":
@@ -503,6 +513,8 @@ class Engine:
         for i, c in enumerate(self._custom_objects):
             with open(os.path.join(input_dir, f"custom_checkpoint_{i}.pkl"), "rb") as f:
                 c.load_state_dict(pickle.load(f))
+        if self.scaler is not None:
+            self.scaler.load_state_dict(torch.load(os.path.join(input_dir, "scaler.pt")))
         rng_path = os.path.join(input_dir, f"random_states_{self.process_index}.pt")
         if os.path.exists(rng_path):
             rng = torch.load(rng_path)

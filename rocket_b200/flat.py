@@ -19,6 +19,8 @@ received a gradient are skipped, as torch.optim skips ``grad is None``.
 """
 from __future__ import annotations
 
+import math
+
 import torch
 
 from rocket_b200.backend import TensorSpec
@@ -38,6 +40,9 @@ class EngineOptimizer:
         # the new parameters to all ranks.  Needs the NVLink exchange path; otherwise the step
         # stays replicated (which is what one GPU is anyway).
         self.sharded = bool(sharded) and engine.num_processes > 1 and engine.wants_p2p()
+        if self.sharded and getattr(engine, "scaler", None) is not None:
+            raise NotImplementedError("sharded optimizer step with mixed_precision='fp16'")
+        self._skipped = False            # fp16: the last step overflowed and was skipped
         self.max_grad_norm: float | None = None
         self.last_grad_norm: torch.Tensor | None = None   # device scalar, for logging
         self._zeroed_by_step = False
@@ -200,7 +205,7 @@ class EngineOptimizer:
 
     @property
     def step_was_skipped(self) -> bool:
-        return False
+        return self._skipped
 
     def zero_grad(self, set_to_none: bool | None = None) -> None:
         if not self.engine.sync_gradients:
@@ -223,10 +228,10 @@ class EngineOptimizer:
             return self.last_grad_norm
         self._adopt_grads()
         plan = self._get_plan()
-        if self.engine.finish_grad_sync(self):
+        if self.engine.finish_grad_sync(self) and self.engine.scaler is None:
             norm = self.engine.backend.l2norm_finalize(plan)
         else:
-            norm = self.engine.backend.l2norm(plan, self.engine.grad_scale(self))
+            norm = self.engine.backend.l2norm(plan, self._read_scale())
         self._pending_clip = float(max_norm)
         self.last_grad_norm = norm
         return norm
@@ -246,9 +251,14 @@ class EngineOptimizer:
                 raise RuntimeError("CUDA-graph capture before the optimizer's first eager step")
             plan = self._get_plan()
             fused_norm = eng.finish_grad_sync(self)  # True: norm partials are in plan.scratch
-            scale = eng.grad_scale(self)
+            scale = self._read_scale()
+            scaler = eng.scaler
+            if scaler is not None:
+                if gp is not None:
+                    raise NotImplementedError("Module(graph=True) with mixed_precision='fp16'")
+                fused_norm = False     # the exchange's partials are of the loss-scaled gradients
             norm = None
-            if max_norm is not None:
+            if max_norm is not None or scaler is not None:
                 if self._pending_clip is not None:
                     norm = self.last_grad_norm
                 elif fused_norm:
@@ -257,6 +267,20 @@ class EngineOptimizer:
                     norm = eng.backend.l2norm(plan, scale)
                 self.last_grad_norm = norm
         self._pending_clip = None
+        if not replay and scaler is not None:
+            # fp16: the norm of the unscaled gradients is also GradScaler's overflow check (any
+            # non-finite element makes it non-finite); reading it is the one host sync
+            # GradScaler.step makes too (found_inf.item()).  Overflow: skip the step, keep the
+            # step counters, clear the gradients, back the scale off.
+            self._skipped = not math.isfinite(float(norm))
+            scaler.update(self._skipped)
+            if self._skipped:
+                self.flat_g.zero_()
+                eng.grad_sync_step_done(self)
+                self._zeroed_by_step = True
+                return
+            if max_norm is None:
+                norm = None
         groups = self._step_groups()
         if self.sharded:
             if gp is not None:
@@ -288,6 +312,14 @@ class EngineOptimizer:
         eng.grad_sync_step_done(self)
         self._zeroed_by_step = True
         self.optimizer._opt_called = True   # what torch's LRScheduler checks before warning
+
+    def _read_scale(self) -> float:
+        """Factor applied to every gradient as the kernels read it: 1/world_size where the
+        exchange left a plain sum, times 1/loss_scale under fp16 (GradScaler's unscale pass,
+        folded in; both are powers of two, so the product is exact)."""
+        scale = self.engine.grad_scale(self)
+        scaler = getattr(self.engine, "scaler", None)
+        return scale * scaler.inv_scale if scaler is not None else scale
 
     def _step_groups(self) -> list[dict]:
         """This step's hyper-parameters per param group (advances the step counters)."""

@@ -35,6 +35,14 @@ CASES = {
                              n_train=64 * 25),
     "lenet_sgd_clip": dict(optimizer="sgd", max_norm=1.0, accum=1, epochs=1, n_train=64 * 20),
     "lenet_adam_l2": dict(optimizer="adam", max_norm=None, accum=3, epochs=1, n_train=64 * 20),
+    # mixed_precision="fp16": torch's GradScaler through the accelerate shim (on the CPU -- real
+    # accelerate wants a GPU for fp16; the scaler arithmetic is the same).  Inputs x128 make the
+    # fp16 weight gradients overflow until the loss scale has backed off: 4-5 skipped steps.
+    "lenet_fp16_adamw_clip": dict(optimizer="adamw", max_norm=0.5, accum=2, epochs=1,
+                                  n_train=64 * 20, sched_step=3, input_scale=128.0,
+                                  mixed_precision="fp16"),
+    "lenet_fp16_sgd": dict(optimizer="sgd", max_norm=None, accum=1, epochs=1, n_train=64 * 20,
+                           sched_step=3, lr=2e-5, input_scale=128.0, mixed_precision="fp16"),
 }
 
 
@@ -66,7 +74,10 @@ def main() -> None:
     torch.set_num_threads(1)
     torch.use_deterministic_algorithms(True)
     here = Path(__file__).resolve().parent
+    only = set(sys.argv[1:])              # optional: regenerate just the named cases
     for name, kwargs in CASES.items():
+        if only and name not in only:
+            continue
         out = run_case(rk, name, kwargs)
         np.savez_compressed(here / f"{name}.npz", **out)
         print(name, "steps", len(out["loss_values"]), "final loss", out["loss_values"][-1],

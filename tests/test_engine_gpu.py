@@ -238,3 +238,106 @@ def test_graph_captured_step_equals_eager_step(name):
     assert [tuple(x) for x in h_g["accuracy"].history] == [tuple(x) for x in h_e["accuracy"].history]
     for (k, a), (_, b) in zip(h_g["net"].named_parameters(), h_e["net"].named_parameters()):
         assert torch.equal(a, b), k
+
+
+# ---- mixed_precision="fp16": dynamic loss scaling ---------------------
+FP16_CASES = {
+    "fp16_adamw_clip": dict(optimizer="adamw", max_norm=0.5, accum=2, epochs=1, n_train=64 * 20,
+                            sched_step=3, input_scale=128.0, mixed_precision="fp16"),
+    "fp16_sgd": dict(optimizer="sgd", max_norm=None, accum=1, epochs=1, n_train=64 * 20,
+                     sched_step=3, lr=2e-5, input_scale=128.0, mixed_precision="fp16"),
+}
+
+
+@pytest.mark.parametrize("name", list(FP16_CASES))
+@pytest.mark.parametrize("arm", list(ARMS))
+def test_fp16_loss_scaling_matches_gradscaler_port_on_gpu(name, arm):
+    """The engine's fp16 path (unscale folded into the kernels' gradient read, overflow check
+    = the norm kernel, host-side GradScaler bookkeeping) against torch.amp.GradScaler driving
+    the port on the same GPU: same skipped steps (lr series), same final loss scale, same
+    counts; parameters bit-exact against the oracle arm where no sqrt/clip is involved."""
+    import rocket_b200 as rk
+    from rocket_b200.engine import Engine
+    from rocket_b200.metrics import Accuracy
+    from rocket_b200.tracking import MemoryTracker
+    kw = FP16_CASES[name]
+    port = looper_port.run_mnist_port(
+        device="cuda", workloads=workloads,
+        optimizer_impl="oracle" if arm == "oracle" else "torch", **kw)
+    engines = []
+    old = rk.Launcher.engine_factory
+    rk.Launcher.engine_factory = staticmethod(lambda **k: engines.append(Engine(**k)) or engines[-1])
+    try:
+        tracker = MemoryTracker("memory")
+        launcher, h = workloads.build_mnist_graph(
+            rk, tracker_backend=tracker, clip_via="kwarg" if kw["max_norm"] else "capsule",
+            accuracy_cls=Accuracy, **kw)
+        launcher.launch()
+    finally:
+        rk.Launcher.engine_factory = old
+    losses = [(s, d["train_loss"]) for s, d in tracker.scalars if "train_loss" in d]
+    lrs = [(s, d["opt.lr.0"]) for s, d in tracker.scalars if "opt.lr.0" in d]
+    assert [v for _, v in lrs] == port["lr_values"]              # the same steps were skipped
+    assert engines[0].scaler.get_scale() == port["scaler"].get_scale()
+    assert engines[0].scaler.state_dict() == port["scaler"].state_dict()
+    assert [s for s, _ in losses] == port["loss_steps"]
+    np.testing.assert_allclose([v for _, v in losses], port["loss_values"], rtol=1e-5)
+    assert [tuple(x) for x in h["accuracy"].history] == \
+        [tuple(x) for x in port["accuracy_history"]]
+    mine = dict(h["net"].named_parameters())
+    for k, want in port["params"].items():
+        got = mine[k].detach().cpu()
+        if arm == "oracle" and kw["max_norm"] is None:
+            assert torch.equal(got, want), f"{k}: not bit-exact against the oracle arm"
+        assert _rel(got, want) <= ARMS[arm], (k, _rel(got, want))
+
+
+def test_fp16_overflow_skips_the_step_and_backs_the_scale_off():
+    """An overflowing backward (inf gradients) must leave parameters, moments and step counts
+    untouched, clear the gradients, halve the scale and report step_was_skipped; the next clean
+    step must equal torch's AdamW + GradScaler on the same gradients."""
+    from rocket_b200.engine import Engine
+    torch.manual_seed(0)
+    eng = Engine(mixed_precision="fp16", stage_batches=False)
+    net = torch.nn.Linear(64, 32).cuda()
+    ref = torch.nn.Linear(64, 32).cuda()
+    ref.load_state_dict(net.state_dict())
+    opt = eng.prepare(torch.optim.AdamW(net.parameters(), lr=1e-2))
+    opt.max_grad_norm = 1.0
+    ref_opt = torch.optim.AdamW(ref.parameters(), lr=1e-2, foreach=False)
+    ref_scaler = torch.amp.GradScaler("cuda")
+    x = torch.randn(16, 64, device="cuda")
+    before = [p.detach().clone() for p in net.parameters()]
+    for it, blow_up in enumerate([False, True, False, False]):
+        factor = float("inf") if blow_up else 1.0
+        with eng.accumulate(net):
+            loss = net(x).pow(2).mean() * factor
+            eng.backward(loss)
+            opt.step()
+            opt.zero_grad()
+        rloss = ref(x).pow(2).mean() * factor
+        ref_scaler.scale(rloss).backward()
+        ref_scaler.unscale_(ref_opt)
+        torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0, foreach=False)
+        ref_scaler.step(ref_opt)
+        ref_scaler.update()
+        ref_opt.zero_grad()
+        assert opt.step_was_skipped == blow_up
+        assert eng.scaler.get_scale() == ref_scaler.get_scale()
+        assert not opt.flat_g.any()
+        if blow_up:
+            assert eng.scaler.get_scale() == 32768.0
+            assert opt._group_step == [1]                    # the skipped step did not count
+    for p, r, b in zip(net.parameters(), ref.parameters(), before):
+        assert not torch.equal(p, b)
+        assert _rel(p.detach(), r.detach()) <= 1e-5
+    sd = opt.state_dict()
+    assert float(sd["state"][0]["step"]) == 3.0
+
+
+def test_fp16_engine_starts_with_gradscaler_defaults():
+    from rocket_b200.engine import Engine
+    eng = Engine(mixed_precision="fp16", stage_batches=False)
+    assert eng.scaler is not None and eng.scaler.get_scale() == 65536.0
+    eng2 = Engine(mixed_precision="bf16", stage_batches=False)
+    assert eng2.scaler is None

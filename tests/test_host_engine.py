@@ -80,6 +80,124 @@ def test_sgd_with_clip_is_bit_exact_vs_reference(rk):
                               gold[f"param/{k}"].view(np.int32)), k
 
 
+FP16_CASES = {
+    "lenet_fp16_adamw_clip": dict(optimizer="adamw", max_norm=0.5, accum=2, epochs=1,
+                                  n_train=64 * 20, sched_step=3, input_scale=128.0,
+                                  mixed_precision="fp16"),
+    "lenet_fp16_sgd": dict(optimizer="sgd", max_norm=None, accum=1, epochs=1, n_train=64 * 20,
+                           sched_step=3, lr=2e-5, input_scale=128.0, mixed_precision="fp16"),
+}
+
+
+@pytest.mark.parametrize("name", list(FP16_CASES))
+@pytest.mark.parametrize("clip_via", ["capsule", "kwarg"])
+def test_fp16_loss_scaling_matches_reference_with_gradscaler(rk, name, clip_via):
+    """mixed_precision="fp16": the reference (through accelerate) runs torch's GradScaler.
+    The goldens contain 4-5 overflowing steps at the start: skipped optimizer steps, skipped
+    scheduler steps (visible in the lr series) and the scale backing off must all line up,
+    and the parameters after training must match (SGD: bit for bit)."""
+    from rocket_b200.tracking import MemoryTracker
+    kw = FP16_CASES[name]
+    if kw["max_norm"] is None and clip_via == "kwarg":
+        pytest.skip("no clipping in this case")
+    gold = np.load(GOLDEN / f"{name}.npz")
+    engines = []
+    factory = rk.Launcher.engine_factory
+    rk.Launcher.engine_factory = staticmethod(lambda **k: engines.append(factory(**k)) or engines[-1])
+    tracker = MemoryTracker("memory")
+    launcher, h = workloads.build_mnist_graph(rk, tracker_backend=tracker, clip_via=clip_via, **kw)
+    launcher.launch()
+    losses = [(s, d["train_loss"]) for s, d in tracker.scalars if "train_loss" in d]
+    lrs = [(s, d["opt.lr.0"]) for s, d in tracker.scalars if "opt.lr.0" in d]
+    assert [v for _, v in lrs] == gold["lr_values"].tolist()       # same steps were skipped
+    assert len(set(gold["lr_values"][:6].tolist())) == 1, "the golden should start with skips"
+    assert [s for s, _ in losses] == gold["loss_steps"].tolist()
+    np.testing.assert_allclose([v for _, v in losses], gold["loss_values"], rtol=2e-6)
+    assert [list(x) for x in h["accuracy"].history] == gold["accuracy_history"].tolist()
+    scaler = engines[0].scaler
+    assert scaler.get_scale() < 65536.0 and scaler.state_dict()["_growth_tracker"] > 0
+    for k, p in h["net"].named_parameters():
+        want = gold[f"param/{k}"]
+        if kw["optimizer"] == "sgd":
+            assert np.array_equal(p.detach().numpy().view(np.int32), want.view(np.int32)), k
+        else:
+            assert np.abs(p.detach().numpy() - want).max() <= 2e-5 * np.abs(want).max(), k
+
+
+def test_loss_scaler_follows_torch_gradscaler_bookkeeping():
+    """scale / growth-tracker trajectory against torch.amp.GradScaler on the same overflow
+    pattern, including growth after growth_interval clean steps and the checkpoint format."""
+    from rocket_b200.scaler import LossScaler
+    pattern = [True, True, False, False, False, True, False, False, False, False, False, False]
+    ref = torch.amp.GradScaler("cpu", init_scale=2.0 ** 10, growth_interval=3)
+    mine = LossScaler(torch.device("cpu"), init_scale=2.0 ** 10, growth_interval=3)
+    assert float(mine.scale(torch.ones(()))) == float(ref.scale(torch.ones(())))   # (lazy init)
+    lin = torch.nn.Linear(2, 1)
+    opt = torch.optim.SGD(lin.parameters(), lr=0.0)
+    for overflow in pattern:
+        for p in lin.parameters():
+            p.grad = torch.full_like(p, float("inf") if overflow else 1.0)
+        ref.step(opt)
+        ref.update()
+        mine.update(overflow)
+        assert mine.get_scale() == ref.get_scale()
+        assert mine.state_dict() == ref.state_dict()
+        assert float(mine._dev_scale) == ref.get_scale()
+        assert mine.inv_scale == float(ref._scale.double().reciprocal().float())
+    other = LossScaler(torch.device("cpu"))
+    other.load_state_dict(ref.state_dict())
+    assert other.state_dict() == ref.state_dict()
+
+
+def test_fp16_overflow_skips_the_step_and_backs_the_scale_off():
+    """Host logic of the fp16 step (same scenario as the GPU test of this name)."""
+    from rocket_b200.engine import Engine
+    torch.manual_seed(0)
+    eng = Engine(backend=HostBackend(), device="cpu", mixed_precision="fp16")
+    net, ref = torch.nn.Linear(64, 32), torch.nn.Linear(64, 32)
+    ref.load_state_dict(net.state_dict())
+    opt = eng.prepare(torch.optim.AdamW(net.parameters(), lr=1e-2))
+    opt.max_grad_norm = 1.0
+    ref_opt = torch.optim.AdamW(ref.parameters(), lr=1e-2, foreach=False)
+    ref_scaler = torch.amp.GradScaler("cpu")
+    x = torch.randn(16, 64)
+    for blow_up in [False, True, False, False]:
+        factor = float("inf") if blow_up else 1.0
+        with eng.accumulate(net):
+            eng.backward(net(x).pow(2).mean() * factor)
+            opt.step()
+            opt.zero_grad()
+        ref_scaler.scale(ref(x).pow(2).mean() * factor).backward()
+        ref_scaler.unscale_(ref_opt)
+        torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0, foreach=False)
+        ref_scaler.step(ref_opt)
+        ref_scaler.update()
+        ref_opt.zero_grad()
+        assert opt.step_was_skipped == blow_up
+        assert eng.scaler.get_scale() == ref_scaler.get_scale()
+        assert not opt.flat_g.any()
+        if blow_up:
+            assert opt._group_step == [1]
+    for p, r in zip(net.parameters(), ref.parameters()):
+        assert np.abs(p.detach().numpy() - r.detach().numpy()).max() <= 1e-6
+    assert float(opt.state_dict()["state"][0]["step"]) == 3.0
+
+
+def test_fp16_scaler_state_is_checkpointed_in_gradscaler_format(tmp_path):
+    from rocket_b200.engine import Engine
+    eng = Engine(backend=HostBackend(), device="cpu", mixed_precision="fp16")
+    eng.scaler.update(True)
+    eng.scaler.update(False)
+    eng.save_state(str(tmp_path))
+    stock = torch.amp.GradScaler("cpu")
+    stock.load_state_dict(torch.load(tmp_path / "scaler.pt"))     # loads into stock torch
+    assert stock.get_scale() == 32768.0 and stock._init_growth_tracker == 1
+    fresh = Engine(backend=HostBackend(), device="cpu", mixed_precision="fp16")
+    fresh.load_state(str(tmp_path))
+    assert fresh.scaler.state_dict() == eng.scaler.state_dict()
+    assert float(fresh.scaler._dev_scale) == 32768.0
+
+
 def test_params_grads_and_state_are_views_of_flat_buffers(rk):
     launcher, h = workloads.build_mnist_graph(rk, optimizer="adamw", epochs=1, n_train=64 * 4,
                                               accum=1)

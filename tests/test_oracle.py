@@ -129,6 +129,12 @@ CASES = {
                              n_train=64 * 25),
     "lenet_sgd_clip": dict(optimizer="sgd", max_norm=1.0, accum=1, epochs=1, n_train=64 * 20),
     "lenet_adam_l2": dict(optimizer="adam", max_norm=None, accum=3, epochs=1, n_train=64 * 20),
+    # fp16 + GradScaler, 4-5 overflowing (skipped) steps at the start
+    "lenet_fp16_adamw_clip": dict(optimizer="adamw", max_norm=0.5, accum=2, epochs=1,
+                                  n_train=64 * 20, sched_step=3, input_scale=128.0,
+                                  mixed_precision="fp16"),
+    "lenet_fp16_sgd": dict(optimizer="sgd", max_norm=None, accum=1, epochs=1, n_train=64 * 20,
+                           sched_step=3, lr=2e-5, input_scale=128.0, mixed_precision="fp16"),
 }
 
 

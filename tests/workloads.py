@@ -50,9 +50,11 @@ class CrossEntropy(nn.Module):
         return F.cross_entropy(batch[2], batch[1])
 
 
-def synthetic_classification(n: int, shape, classes: int, seed: int):
+def synthetic_classification(n: int, shape, classes: int, seed: int, input_scale: float = 1.0):
     g = torch.Generator().manual_seed(seed)
     x = torch.randn((n, *shape), generator=g)
+    if input_scale != 1.0:     # large inputs: fp16 weight gradients overflow until the loss
+        x = x * input_scale    # scale has backed off (exercises GradScaler's skipped steps)
     y = torch.randint(0, classes, (n,), generator=g)
     return torch.utils.data.TensorDataset(x, y)
 
@@ -100,7 +102,8 @@ def make_user_clip(rk):
 def build_mnist_graph(rk, *, seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_size=64,
                       optimizer="adamw", max_norm=None, accum=2, epochs=2, sched_step=5,
                       tracker_backend=None, accuracy_cls=None, clip_via="capsule",
-                      lr=1e-3, net=None, opt_kwargs=None, graph=False):
+                      lr=1e-3, net=None, opt_kwargs=None, graph=False, mixed_precision=None,
+                      input_scale=1.0):
     """Returns (launcher, handles) -- handles: net, opt, sched, accuracy, tracker_backend."""
     torch.manual_seed(seed)
     net = net if net is not None else LeNet()
@@ -116,8 +119,8 @@ def build_mnist_graph(rk, *, seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_s
     else:
         raise ValueError(optimizer)
     sched = torch.optim.lr_scheduler.StepLR(opt, sched_step, gamma=0.5)
-    train = synthetic_classification(n_train, (1, 28, 28), 10, seed + 1)
-    val = synthetic_classification(n_val, (1, 28, 28), 10, seed + 2)
+    train = synthetic_classification(n_train, (1, 28, 28), 10, seed + 1, input_scale)
+    val = synthetic_classification(n_val, (1, 28, 28), 10, seed + 2, input_scale)
     accuracy = (accuracy_cls or make_user_accuracy(rk))()
     inner = [rk.Loss(objective=CrossEntropy())]
     if max_norm is not None and clip_via == "capsule":
@@ -139,6 +142,7 @@ def build_mnist_graph(rk, *, seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_s
         [rk.Looper(train_caps, tag="train"),
          rk.Looper(val_caps, tag="val", grad_enabled=False)],
         num_epochs=epochs, gradient_accumulation_steps=accum,
-        destroy_process_group_after_launch=False)
+        destroy_process_group_after_launch=False,
+        **(dict(mixed_precision=mixed_precision) if mixed_precision else {}))
     return launcher, dict(net=net, opt=opt, sched=sched, accuracy=accuracy,
                           tracker=tracker_backend)
