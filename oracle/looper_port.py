@@ -181,6 +181,23 @@ def new_state() -> dict:
                 opt_step=0, accuracy_history=[])
 
 
+def wrap_autocast_forward(net, device, autocast_dtype) -> None:
+    """What accelerate's prepare_model does to a module under mixed precision (reached from
+    rocket/core/module.py:106): forward runs under autocast and its low-precision outputs are
+    converted to fp32 -- so the objective sees fp32 logits.  (On CUDA, cross_entropy of fp16
+    logits and of the same logits converted to fp32 differ in the last digits.)"""
+    if autocast_dtype is None:
+        return
+    inner = net.forward
+
+    def forward(*a, **k):
+        with torch.autocast(device_type=torch.device(device).type, dtype=autocast_dtype):
+            out = inner(*a, **k)
+        return [t.float() if isinstance(t, torch.Tensor) and t.dtype == autocast_dtype else t
+                for t in out]
+    net.forward = forward
+
+
 def run_mnist_port(*, device="cpu", seed=0, n_train=64 * 24, n_val=64 * 5 + 13, batch_size=64,
                    optimizer="adamw", max_norm=None, accum=2, epochs=2, sched_step=5, lr=1e-3,
                    net=None, workloads=None, optimizer_impl="torch", mixed_precision=None,
@@ -209,6 +226,7 @@ def run_mnist_port(*, device="cpu", seed=0, n_train=64 * 24, n_val=64 * 5 + 13, 
     scaler = torch.amp.GradScaler(torch.device(device).type) if mixed_precision == "fp16" \
         else None
     net.to(device)
+    wrap_autocast_forward(net, device, amp_dtype)
     objective = workloads.CrossEntropy()
     tl = torch.utils.data.DataLoader(train, batch_size=batch_size, shuffle=False)
     vl = torch.utils.data.DataLoader(val, batch_size=batch_size, shuffle=False)
@@ -257,15 +275,7 @@ def run_generic_port(net, objective, opt, batches, *, accum: int, max_norm, devi
         opt._opt_called = True
         opt = OracleOptimizer(opt, max_norm)
     net.to(device)
-    if autocast_dtype is not None:
-        inner = net.forward
-
-        def forward(*a, **k):
-            with torch.autocast(device_type=torch.device(device).type, dtype=autocast_dtype):
-                out = inner(*a, **k)
-            return [t.float() if isinstance(t, torch.Tensor) and t.dtype == autocast_dtype else t
-                    for t in out]
-        net.forward = forward
+    wrap_autocast_forward(net, device, autocast_dtype)
     state = new_state()
     train_epoch(net, objective, opt, None, batches, accum=accum, max_norm=max_norm,
                 device=device, state=state, autocast_dtype=autocast_dtype)

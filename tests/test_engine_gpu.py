@@ -281,7 +281,11 @@ def test_fp16_loss_scaling_matches_gradscaler_port_on_gpu(name, arm):
     assert engines[0].scaler.get_scale() == port["scaler"].get_scale()
     assert engines[0].scaler.state_dict() == port["scaler"].state_dict()
     assert [s for s, _ in losses] == port["loss_steps"]
-    np.testing.assert_allclose([v for _, v in losses], port["loss_values"], rtol=1e-5)
+    # (torch_cuda arm: torch's CUDA AdamW rounds differently from its CPU kernels -- see ARMS --
+    # and the fp16 forward amplifies that into the loss after a few steps: measured 2.1e-5)
+    np.testing.assert_allclose([v for _, v in losses], port["loss_values"], rtol=ARMS[arm])
+    if arm == "oracle":
+        assert [v for _, v in losses] == port["loss_values"]
     assert [tuple(x) for x in h["accuracy"].history] == \
         [tuple(x) for x in port["accuracy_history"]]
     mine = dict(h["net"].named_parameters())
