@@ -284,7 +284,7 @@ def test_fp16_loss_scaling_matches_gradscaler_port_on_gpu(name, arm):
     # (torch_cuda arm: torch's CUDA AdamW rounds differently from its CPU kernels -- see ARMS --
     # and the fp16 forward amplifies that into the loss after a few steps: measured 2.1e-5)
     np.testing.assert_allclose([v for _, v in losses], port["loss_values"], rtol=ARMS[arm])
-    if arm == "oracle":
+    if arm == "oracle" and kw["max_norm"] is None:
         assert [v for _, v in losses] == port["loss_values"]
     assert [tuple(x) for x in h["accuracy"].history] == \
         [tuple(x) for x in port["accuracy_history"]]
