@@ -450,7 +450,7 @@ def run_ours(args) -> dict:
             "note": "bus GB/s = 2(W-1)/W x bytes / kernel time = bytes crossing NVLink per "
                     "direction per GPU; peak = measured peer-copy bandwidth (B200_PROFILING.md); "
                     "kernel time includes waiting for the slowest rank's backward"}
-    if world > 1 and not args.no_optstep and out["config"]["grad_sync"] == "P2PGradSync":
+    if world > 1 and not args.no_optstep and out["config"]["grad_sync"].startswith("P2PGradSync"):
         out["optstep"] = optstep_microbench_dp(peak, rank, world, local)
     if rank == 0 and world == 1 and not args.no_optstep:
         out["optstep"] = optstep_microbench(peak)

@@ -75,7 +75,10 @@ class Module(Dispatcher):
         engine = self._accelerator
         if engine.device.type != "cuda" or not hasattr(engine, "graph_pass"):
             return False
-        # multi-GPU: only the hand-written NVLink exchange is replayable (device-side epochs)
+        if getattr(engine, "scaler", None) is not None:
+            return False     # fp16: the overflow decision is a host read between norm and step
+        # multi-GPU: only the hand-written NVLink exchange is replayable (device-side epochs);
+        # with a sharded optimizer step the step stays eager
         return engine.num_processes == 1 or (
             bool(engine.grad_sync_kinds)
             and all(k == "P2PGradSync" for k in engine.grad_sync_kinds))
