@@ -21,6 +21,17 @@ WS2_CASES = {
 }
 
 
+# fp16 + GradScaler under DDP: every rank runs its own scaler on the averaged (still scaled)
+# gradients, so all ranks skip the same steps.  Kept apart from WS2_CASES, which the GPU tests
+# parametrize over.
+WS2_FP16_CASES = {
+    "ws2_fp16_sgd": dict(optimizer="sgd", max_norm=None, accum=1, epochs=1, n_train=64 * 24,
+                         n_val=64 * 2 + 5, sched_step=3, lr=2e-5, input_scale=128.0,
+                         mixed_precision="fp16"),
+}
+ALL_CASES = {**WS2_CASES, **WS2_FP16_CASES}
+
+
 def _env(rank: int, world: int, port: int) -> None:
     os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
                       MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), TQDM_DISABLE="1",
@@ -47,7 +58,7 @@ def reference_worker(rank: int, world: int, port: int, case: str, out_dir: str) 
     import workloads
     from accelerate.tracking import MemoryTracker
     tracker = MemoryTracker("memory")
-    launcher, h = workloads.build_mnist_graph(rk, tracker_backend=tracker, **WS2_CASES[case])
+    launcher, h = workloads.build_mnist_graph(rk, tracker_backend=tracker, **ALL_CASES[case])
     launcher.launch()
     if rank == 0:
         np.savez_compressed(Path(out_dir) / f"{case}.npz", **_collect(h, tracker))
@@ -69,7 +80,7 @@ def engine_worker(rank: int, world: int, port: int, case: str, out_dir: str,
     rk.Launcher.engine_factory = staticmethod(
         lambda **kw: Engine(backend=HostBackend(), device="cpu", **kw))
     tracker = MemoryTracker("memory")
-    kw = dict(WS2_CASES[case])
+    kw = dict(ALL_CASES[case])
     launcher, h = workloads.build_mnist_graph(
         rk, tracker_backend=tracker, clip_via="kwarg" if kw["max_norm"] else "capsule",
         accuracy_cls=Accuracy if device_metric else None, **kw)

@@ -14,6 +14,9 @@ import dist_worker  # noqa: E402
 
 if __name__ == "__main__":
     here = str(Path(__file__).resolve().parent)
-    for i, case in enumerate(dist_worker.WS2_CASES):
+    only = set(sys.argv[1:])              # optional: regenerate just the named cases
+    for i, case in enumerate(dist_worker.ALL_CASES):
+        if only and case not in only:
+            continue
         mp.spawn(dist_worker.reference_worker, args=(2, 29610 + i, case, here), nprocs=2, join=True)
         print("wrote", case)

@@ -47,6 +47,25 @@ def test_two_ranks_match_reference_under_ddp(case, device_metric, tmp_path):
             assert np.abs(r0[k] - want).max() <= 2e-5 * np.abs(want).max(), k
 
 
+def test_two_ranks_fp16_skip_the_same_steps_as_reference_under_ddp(tmp_path):
+    """mixed_precision="fp16" on two ranks: the golden is the unmodified reference under DDP
+    with one torch GradScaler per rank; its first steps overflow.  Both engine ranks must skip
+    exactly those steps (lr series; the scheduler moves W times per real step) and end on the
+    reference's parameters bit for bit (SGD: no sqrt between the oracle and torch)."""
+    case = "ws2_fp16_sgd"
+    gold = np.load(GOLDEN / f"{case}.npz")
+    r0, r1 = _run(case, tmp_path, True)
+    assert len(set(gold["lr_values"][:5].tolist())) == 1, "the golden should start with skips"
+    assert r0["lr_values"].tolist() == gold["lr_values"].tolist()
+    assert r0["loss_steps"].tolist() == gold["loss_steps"].tolist()
+    np.testing.assert_allclose(r0["loss_values"], gold["loss_values"], rtol=1e-6)
+    assert r0["accuracy_history"].tolist() == gold["accuracy_history"].tolist()
+    for k in gold.files:
+        if k.startswith("param/"):
+            assert np.array_equal(r0[k].view(np.int32), r1[k].view(np.int32)), k
+            assert np.array_equal(r0[k].view(np.int32), gold[k].view(np.int32)), k
+
+
 def test_sharded_batch_sampler_even_batches():
     from rocket_b200.staging import ShardedBatchSampler
     from torch.utils.data import BatchSampler, SequentialSampler
