@@ -551,8 +551,10 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
     # (P2P loads / stores at every W, like the engine: comm.P2PGradSync)
     table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8, device=dev)
     host_table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8).pin_memory()
-    m.zero_()
-    v.zero_()
+    del m, v                                   # the sharded step keeps 1/W of the moments
+    torch.cuda.empty_cache()
+    shard = -(-plan.n_chunks_norm // world) * plan.chunk_norm
+    sm, sv = torch.zeros(shard, device=dev), torch.zeros(shard, device=dev)
     sx, ss = [], []
     for i in range(warmup + steps):
         torch.manual_seed(1000 * i + rank)
@@ -566,7 +568,7 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
         be.comm_reduce_scatter_norm(comm, plan, 0, plan.n_chunks_norm, 0, 0, stream, False)
         norm = be.l2norm_finalize(plan)
         e[1].record()
-        be.comm_sharded_step(comm, plan, "adamw", table.data_ptr(), norm, 1.0, 0, False)
+        be.comm_sharded_step(comm, plan, "adamw", table.data_ptr(), norm, 1.0, 0, False, sm, sv)
         e[2].record()
         torch.cuda.synchronize()
         if i >= warmup:
@@ -578,7 +580,7 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
     t_x, t_s, s_x, s_s = (float(x) for x in t)
     dist.barrier()
     be.comm_destroy(comm)
-    del keep, p, m, v, g, plan, arena
+    del keep, p, sm, sv, g, plan, arena
     torch.cuda.ipc_collect()
     torch.cuda.empty_cache()
     bus = 2 * (world - 1) / world * 4 * n / (t_x * 1e-3) / 1e9
@@ -588,7 +590,8 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
             "step_kernel_ms": round(t_s, 4),
             "step_kernel_gbs": round(ALGO_BYTES_STEP * n / (t_s * 1e-3) / 1e9, 1),
             "ms_per_optimizer_step": round(t_x + t_s, 4),
-            "sharded": {"reduce_scatter_plus_norm_ms": round(s_x, 4),
+            "sharded": {"moment_bytes_per_gpu": 8 * shard,
+                        "reduce_scatter_plus_norm_ms": round(s_x, 4),
                         "sharded_step_ms": round(s_s, 4),
                         "ms_per_optimizer_step": round(s_x + s_s, 4)},
             "step_kernel_frac_of_measured_peak":

@@ -260,15 +260,22 @@ int rk_comm_destroy(rk_comm* comm);
  * zero-fills the whole local gradient buffer, and ends with a barrier among the ranks.  Per
  * element the arithmetic is the replicated step's, so parameters are bit-identical to data
  * parallelism; optimizer work and moment traffic per GPU shrink by W.  table_dev is the
- * RK_STEP_TABLE_BYTES table written by rk_adam_table_write / rk_sgd_table_write; the m / v
- * pointers of chunks a rank does not own are never touched.  Uses barrier slot
- * RK_COMM_MAX_BUCKETS - 1: exchanges that share the communicator must use lower buckets.  */
+ * RK_STEP_TABLE_BYTES table written by rk_adam_table_write / rk_sgd_table_write.
+ * Moments: with shard_m / shard_v == NULL the plan's per-tensor m / v buffers are used (full
+ * size; the parts of chunks a rank does not own are never touched).  Otherwise they are this
+ * rank's compact moment shards, 1/W of the full size: the moments of owned norm chunk c occupy
+ * elements [(c / W) * chunk_norm, ... + chunk length) -- ceil(n_chunks_norm / W) * chunk_norm
+ * floats each, 16-byte aligned, zero-filled before the first step -- and the plan's m / v
+ * pointers are ignored (shard_v is ignored for SGD; shard_m == NULL with plan m == NULL means
+ * plain SGD without momentum).  Uses barrier slot RK_COMM_MAX_BUCKETS - 1: exchanges that
+ * share the communicator must use lower buckets.                                            */
 int rk_comm_reduce_scatter_norm(rk_comm* comm, const void* plan_host, const void* plan_dev,
                                 int chunk_lo, int chunk_hi, int bucket, int max_ctas,
                                 int use_multicast, void* stream);
 int rk_comm_sharded_step(rk_comm* comm, const void* plan_host, const void* plan_dev,
-                         int optimizer, const void* table_dev, const float* total_norm_dev,
-                         float max_norm, int max_ctas, int use_multicast, void* stream);
+                         int optimizer, const void* table_dev, float* shard_m, float* shard_v,
+                         const float* total_norm_dev, float max_norm, int max_ctas,
+                         int use_multicast, void* stream);
 
 /* ---- K5: pinned-ring batch stager ---------------------------------------------------
  * Replaces the blocking pageable `Tensor.to(device)` of rocket/utils/torch.py:50-51

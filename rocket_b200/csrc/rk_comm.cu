@@ -370,6 +370,7 @@ template <class Op, class Table, int W, bool MC>
 __global__ void __launch_bounds__(COMM_THREADS, 3)
 rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
                        const char* __restrict__ plan, const Table* __restrict__ dtable,
+                       float* __restrict__ shard_m, float* __restrict__ shard_v,
                        const float* __restrict__ total_norm, float max_norm, int bucket) {
   __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   const int tid = threadIdx.x;
@@ -419,9 +420,12 @@ rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
       }
       continue;
     }
-    float* M = d.m + base;
-    float* V = Op::kHasV ? d.v + base : nullptr;
-    const bool has_m = d.m != nullptr;
+    // moments: compact per-rank buffers (owned chunk c lives in slot c / W = this row), or the
+    // plan's full-size per-tensor buffers
+    const int64_t slot = (int64_t)k * chunk;
+    float* M = shard_m ? shard_m + slot : d.m + base;
+    float* V = !Op::kHasV ? nullptr : (shard_v ? shard_v + slot : d.v + base);
+    const bool has_m = shard_m != nullptr || d.m != nullptr;
     const unsigned long long poff =
         (unsigned long long)(reinterpret_cast<char*>(P) - peers.arena[rank]);
     auto put_p4 = [&](int i, const float4& v) {
@@ -491,10 +495,15 @@ rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
 
 template <class Op, class Table>
 static int launch_sharded(rk_comm* c, const void* plan_host, const void* plan_dev,
-                          const void* table_dev, const float* total_norm_dev, float max_norm,
-                          int max_ctas, int use_multicast, void* stream) {
+                          const void* table_dev, float* shard_m, float* shard_v,
+                          const float* total_norm_dev, float max_norm, int max_ctas,
+                          int use_multicast, void* stream) {
   RK_REQUIRE(c && plan_host && plan_dev && table_dev, RK_ERR_INVALID,
              "rk_comm_sharded_step: null argument");
+  RK_REQUIRE(!Op::kHasV || (shard_m == nullptr) == (shard_v == nullptr), RK_ERR_INVALID,
+             "rk_comm_sharded_step: shard_m and shard_v must both be given or both be NULL");
+  RK_REQUIRE((((uintptr_t)shard_m | (uintptr_t)shard_v) & 15) == 0, RK_ERR_INVALID,
+             "rk_comm_sharded_step: moment shards must be 16-byte aligned");
   const rk_plan_header* h = (const rk_plan_header*)plan_host;
   RK_REQUIRE(h->magic == RK_PLAN_MAGIC, RK_ERR_INVALID, "rk_comm_sharded_step: bad plan magic");
   int grid = max_ctas > 0 ? max_ctas : 3 * c->sms;
@@ -507,7 +516,7 @@ static int launch_sharded(rk_comm* c, const void* plan_host, const void* plan_de
 #define RK_LAUNCH(WW, MC)                                                                     \
   rk_sharded_step_kernel<Op, Table, WW, MC><<<grid, COMM_THREADS, 0, s>>>(                   \
       c->peers, c->mc_arena, c->rank, (const char*)plan_dev, (const Table*)table_dev,         \
-      total_norm_dev, max_norm, bucket)
+      shard_m, shard_v, total_norm_dev, max_norm, bucket)
   switch (c->world) {
     case 2: if (mc) RK_LAUNCH(2, true); else RK_LAUNCH(2, false); break;
     case 4: if (mc) RK_LAUNCH(4, true); else RK_LAUNCH(4, false); break;
@@ -520,15 +529,17 @@ static int launch_sharded(rk_comm* c, const void* plan_host, const void* plan_de
 }
 
 extern "C" int rk_comm_sharded_step(rk_comm* c, const void* plan_host, const void* plan_dev,
-                                    int optimizer, const void* table_dev,
-                                    const float* total_norm_dev, float max_norm, int max_ctas,
-                                    int use_multicast, void* stream) {
+                                    int optimizer, const void* table_dev, float* shard_m,
+                                    float* shard_v, const float* total_norm_dev, float max_norm,
+                                    int max_ctas, int use_multicast, void* stream) {
   if (optimizer == 0)
-    return launch_sharded<AdamOp, AdamTable>(c, plan_host, plan_dev, table_dev, total_norm_dev,
-                                             max_norm, max_ctas, use_multicast, stream);
+    return launch_sharded<AdamOp, AdamTable>(c, plan_host, plan_dev, table_dev, shard_m, shard_v,
+                                             total_norm_dev, max_norm, max_ctas, use_multicast,
+                                             stream);
   if (optimizer == 1)
-    return launch_sharded<SgdOp, SgdTable>(c, plan_host, plan_dev, table_dev, total_norm_dev,
-                                           max_norm, max_ctas, use_multicast, stream);
+    return launch_sharded<SgdOp, SgdTable>(c, plan_host, plan_dev, table_dev, shard_m, shard_v,
+                                           total_norm_dev, max_norm, max_ctas, use_multicast,
+                                           stream);
   RK_REQUIRE(false, RK_ERR_INVALID, "rk_comm_sharded_step: optimizer %d (0 = Adam(W), 1 = SGD)",
              optimizer);
 }

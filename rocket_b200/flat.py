@@ -116,9 +116,14 @@ class EngineOptimizer:
             self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
         self._needs_m = self._kind != "sgd" or any(
             g.get("momentum", 0) != 0 for g in self.optimizer.param_groups)
-        self.flat_m = torch.zeros(off, dtype=torch.float32, device=dev) if self._needs_m else None
-        self.flat_v = torch.zeros(off, dtype=torch.float32, device=dev) \
-            if self._kind != "sgd" else None
+        # Moments: full-size flat buffers, or -- sharded step -- this rank's compact shards
+        # (1/W of that), allocated below once the chunk layout is known.
+        self.flat_m = self.flat_v = self.shard_m = self.shard_v = None
+        if not self.sharded:
+            if self._needs_m:
+                self.flat_m = torch.zeros(off, dtype=torch.float32, device=dev)
+            if self._kind != "sgd":
+                self.flat_v = torch.zeros(off, dtype=torch.float32, device=dev)
         self._views_p, self._views_g, self._views_m, self._views_v = [], [], [], []
         with torch.no_grad():
             for p, o in zip(self._params, self._offsets):
@@ -128,7 +133,8 @@ class EngineOptimizer:
                 p.data = vp
                 self._views_p.append(vp)
                 self._views_g.append(self.flat_g[o:o + n].view(p.shape))
-                self._views_m.append(self.flat_m[o:o + n].view(p.shape) if self._needs_m else None)
+                self._views_m.append(self.flat_m[o:o + n].view(p.shape)
+                                     if self.flat_m is not None else None)
                 self._views_v.append(self.flat_v[o:o + n].view(p.shape)
                                      if self.flat_v is not None else None)
         self._grad_ptr = [v.data_ptr() for v in self._views_g]
@@ -137,61 +143,83 @@ class EngineOptimizer:
         self._plan = None
         self._table_ring = None
         self._dev_table = torch.zeros(4096, dtype=torch.uint8, device=dev)
+        if self.sharded:
+            plan = self._get_plan()        # the chunk layout depends on the sizes only
+            self._shard_rows = -(-plan.n_chunks_norm // self.engine.num_processes)
+            n = self._shard_rows * plan.chunk_norm
+            if self._needs_m:
+                self.shard_m = torch.zeros(n, dtype=torch.float32, device=dev)
+            if self._kind != "sgd":
+                self.shard_v = torch.zeros(n, dtype=torch.float32, device=dev)
         self._import_state()
 
     def _import_state(self) -> None:
         """Adopt state the wrapped optimizer already holds (resume / prior training)."""
-        found = False
         for i, p in enumerate(self._params):
             st = self.optimizer.state.get(p)
             if not st:
                 continue
-            found = True
             gi = self._group_of[i]
             if "step" in st:
                 self._group_step[gi] = max(self._group_step[gi], int(float(st["step"])))
             if self._kind == "sgd":
                 buf = st.get("momentum_buffer")
                 if buf is not None and self._needs_m:
-                    self._views_m[i].copy_(buf)
-                    st["momentum_buffer"] = self._views_m[i]
+                    if self.sharded:
+                        self._scatter(i, buf, self.shard_m)
+                    else:
+                        self._views_m[i].copy_(buf)
+                        st["momentum_buffer"] = self._views_m[i]
                     self._group_step[gi] = max(self._group_step[gi], 1)
-            else:
-                if "exp_avg" in st:
+            elif "exp_avg" in st:
+                if self.sharded:
+                    self._scatter(i, st["exp_avg"], self.shard_m)
+                    self._scatter(i, st["exp_avg_sq"], self.shard_v)
+                else:
                     self._views_m[i].copy_(st["exp_avg"])
                     self._views_v[i].copy_(st["exp_avg_sq"])
                     st["exp_avg"], st["exp_avg_sq"] = self._views_m[i], self._views_v[i]
-        if self.sharded and found:
-            for flat in (self.flat_m, self.flat_v):
-                if flat is not None:
-                    self._zero_unowned(flat)
 
-    # ---- sharded step: who owns what ---------------------------------------------------------
-    def _zero_unowned(self, flat: torch.Tensor) -> None:
-        """Keep only this rank's chunks of a moment buffer (norm chunk c belongs to rank
-        c % W, as in the exchange kernel); the rest is held at zero, which is what lets
-        ``_gathered`` rebuild the full buffer with one integer SUM."""
+    # ---- sharded step: compact moment shards ---------------------------------------------------
+    # Norm chunk c (global index over all tensors, plan.prefix_norm) belongs to rank c % W, as
+    # in the exchange kernel, and its moments occupy slot c // W of that rank's shard; a slot
+    # is chunk_norm floats (a tensor's short last chunk leaves the rest of its slot unused).
+    def _scatter(self, i: int, full: torch.Tensor, shard: torch.Tensor) -> None:
+        """This rank's chunks of parameter i's full moment tensor -> its shard slots."""
         plan = self._get_plan()
         world, rank = self.engine.num_processes, self.engine.process_index
-        chunk, prefix = plan.chunk_norm, plan.prefix_norm
-        for i, (p, o) in enumerate(zip(self._params, self._offsets)):
-            n, c0 = p.numel(), int(prefix[i])
-            full = n // chunk
-            if full:
-                rows = flat[o:o + full * chunk].view(full, chunk)
-                for k in range(world):
-                    if k != rank:
-                        rows[(k - c0) % world::world].zero_()
-            if n % chunk and (c0 + full) % world != rank:
-                flat[o + full * chunk:o + n].zero_()
+        chunk, c0, n = plan.chunk_norm, int(plan.prefix_norm[i]), self._params[i].numel()
+        n_chunks = -(-n // chunk)
+        if n_chunks == 0:
+            return
+        padded = torch.zeros(n_chunks * chunk, dtype=torch.float32, device=shard.device)
+        padded[:n] = full.detach().reshape(-1).to(shard.device)
+        j0 = (rank - c0) % world
+        own = padded.view(n_chunks, chunk)[j0::world]
+        if own.shape[0]:
+            k0 = (c0 + j0) // world
+            shard.view(-1, chunk)[k0:k0 + own.shape[0]] = own
 
-    def _gathered(self, flat: torch.Tensor) -> torch.Tensor:
-        """Collective: the full moment buffer, bit for bit (every element is non-zero on at
-        most one rank, so summing the bit patterns as integers reproduces the owner's)."""
+    @staticmethod
+    def _interleave(shards: torch.Tensor, chunk: int) -> torch.Tensor:
+        """[W, rows * chunk] (one shard per rank) -> [rows * W, chunk] in global chunk order."""
+        world = shards.shape[0]
+        return shards.view(world, -1, chunk).permute(1, 0, 2).reshape(-1, chunk)
+
+    def _gather_chunks(self, shard: torch.Tensor) -> torch.Tensor:
+        """Collective: every rank's shard, as one table of chunks in global order."""
         import torch.distributed as dist
-        full = flat.clone()
-        dist.all_reduce(full.view(torch.int32), op=dist.ReduceOp.SUM)
-        return full
+        world = self.engine.num_processes
+        out = torch.empty(world, shard.numel(), dtype=shard.dtype, device=shard.device)
+        dist.all_gather_into_tensor(out, shard)
+        return self._interleave(out, self._get_plan().chunk_norm)
+
+    def _assemble(self, i: int, chunks: torch.Tensor) -> torch.Tensor:
+        """Parameter i's full moment tensor out of the table ``_gather_chunks`` returns."""
+        plan = self._get_plan()
+        p = self._params[i]
+        c0, c1 = int(plan.prefix_norm[i]), int(plan.prefix_norm[i + 1])
+        return chunks[c0:c1].reshape(-1)[:p.numel()].view(p.shape).clone()
 
     # ---- the AcceleratedOptimizer surface ---------------------------------------------------
     @property
@@ -293,7 +321,7 @@ class EngineOptimizer:
             eng.backend.comm_sharded_step(
                 sync._comm, plan, self._kind, self._dev_table.data_ptr(), norm,
                 float(max_norm) if max_norm is not None else 0.0, sync.step_ctas,
-                sync.use_multicast)
+                sync.use_multicast, self.shard_m, self.shard_v)
         elif gp is None:
             fn = eng.backend.sgd_step if self._kind == "sgd" else eng.backend.adam_step
             fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)
@@ -397,8 +425,10 @@ class EngineOptimizer:
     def _get_plan(self):
         if self._plan is None:
             specs = [TensorSpec(p=self._views_p[i].reshape(-1), g=self._views_g[i].reshape(-1),
-                                m=self._views_m[i].reshape(-1) if self._needs_m else None,
-                                v=self._views_v[i].reshape(-1) if self.flat_v is not None else None,
+                                m=self._views_m[i].reshape(-1)
+                                if self._views_m[i] is not None else None,
+                                v=self._views_v[i].reshape(-1)
+                                if self._views_v[i] is not None else None,
                                 group=self._group_of[i], skip=not self._adopted[i])
                      for i in range(len(self._params))]
             if self._scratch_view is not None:
@@ -411,13 +441,12 @@ class EngineOptimizer:
     def _export_state(self) -> None:
         views_m, views_v = self._views_m, self._views_v
         if self.sharded:     # collective: every rank has to get here
-            def views(flat):
-                if flat is None:
+            def views(shard):
+                if shard is None:
                     return [None] * len(self._params)
-                full = self._gathered(flat)
-                return [full[o:o + p.numel()].view(p.shape)
-                        for p, o in zip(self._params, self._offsets)]
-            views_m, views_v = views(self.flat_m), views(self.flat_v)
+                chunks = self._gather_chunks(shard)
+                return [self._assemble(i, chunks) for i in range(len(self._params))]
+            views_m, views_v = views(self.shard_m), views(self.shard_v)
         for i, p in enumerate(self._params):
             if not self._adopted[i]:
                 continue

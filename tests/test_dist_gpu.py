@@ -252,7 +252,7 @@ def test_fused_allreduce_norm_kernel_against_nccl(world, path, tmp_path):
 
 
 def _sharded_step_worker(rank: int, world: int, port: int, out_dir: str, multicast: bool,
-                         kind: str) -> None:
+                         kind: str, compact: bool) -> None:
     os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
                       MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     root = Path(__file__).resolve().parent.parent
@@ -277,13 +277,14 @@ def _sharded_step_worker(rank: int, world: int, port: int, out_dir: str, multica
     flat_g = arena[sig + scratch:sig + scratch + 4 * total].view(torch.float32)
     flat_p = arena[sig + scratch + 4 * total:].view(torch.float32)
     sgd = kind == "sgd"
-    flat_m = torch.zeros(total, device=dev)
-    flat_v = None if sgd else torch.zeros(total, device=dev)
+    # moments: full-size per-tensor buffers in the plan, or this rank's compact shards
+    flat_m = None if compact else torch.zeros(total, device=dev)
+    flat_v = None if compact or sgd else torch.zeros(total, device=dev)
     ref_p, ref_g, ref_m = (torch.zeros(total, device=dev) for _ in range(3))
     ref_v = None if sgd else torch.zeros(total, device=dev)
 
     def specs_of(p, g, m, v):
-        return [TensorSpec(p=p[o:o + n], g=g[o:o + n], m=m[o:o + n],
+        return [TensorSpec(p=p[o:o + n], g=g[o:o + n], m=None if m is None else m[o:o + n],
                            v=None if v is None else v[o:o + n], group=gi)
                 for o, n, gi in zip(offs, sizes, groups_of)]
     plan = be.make_plan(specs_of(flat_p, flat_g, flat_m, flat_v), scratch=arena[sig:sig + scratch])
@@ -307,10 +308,17 @@ def _sharded_step_worker(rank: int, world: int, port: int, out_dir: str, multica
     dist.barrier()
     stream = torch.cuda.current_stream().cuda_stream
     half = plan.n_chunks_norm // 2
+    chunk = plan.chunk_norm
+    rows = -(-plan.n_chunks_norm // world)
+    shard_m = torch.zeros(rows * chunk, device=dev) if compact else None
+    shard_v = torch.zeros(rows * chunk, device=dev) if compact and not sgd else None
     owner = torch.zeros(total, dtype=torch.bool, device=dev)       # elements this rank owns
+    slot_of = torch.zeros(total, dtype=torch.int64, device=dev)    # ... and their shard position
     for i, (o, n) in enumerate(zip(offs, sizes)):
-        c = torch.arange(n, device=dev) // plan.chunk_norm + int(plan.prefix_norm[i])
+        e = torch.arange(n, device=dev)
+        c = e // chunk + int(plan.prefix_norm[i])
         owner[o:o + n] = (c % world) == rank
+        slot_of[o:o + n] = (c // world) * chunk + e % chunk
     for it in range(3):
         torch.manual_seed(100 * it + rank)
         flat_g.zero_()
@@ -345,19 +353,27 @@ def _sharded_step_worker(rank: int, world: int, port: int, out_dir: str, multica
         be.step_table_write(kind, groups, host_table)
         table.copy_(host_table, non_blocking=True)
         be.comm_sharded_step(comm, plan, kind, table.data_ptr(), norm_b if max_norm else None,
-                             max_norm, 0, multicast)
+                             max_norm, 0, multicast, shard_m, shard_v)
         torch.cuda.synchronize()
         assert torch.equal(norm_a, norm_b), (it, float(norm_a), float(norm_b))
         assert torch.equal(flat_p.view(torch.int32), ref_p.view(torch.int32)), \
             (it, int((flat_p != ref_p).sum()))
         assert not flat_g.any(), it
-        pairs = [(flat_m, ref_m)] + ([] if sgd else [(flat_v, ref_v)])
-        for mine_s, ref_s in pairs:
-            assert torch.equal(mine_s[owner].view(torch.int32), ref_s[owner].view(torch.int32)), it
-            assert not mine_s[~owner].any(), it           # other ranks' chunks are never touched
-            full = mine_s.clone()
-            dist.all_reduce(full.view(torch.int32))
-            assert torch.equal(full.view(torch.int32), ref_s.view(torch.int32)), it
+        if compact:
+            pairs = [(shard_m, ref_m)] + ([] if sgd else [(shard_v, ref_v)])
+            for shard, ref_s in pairs:
+                # owned elements sit in slot c // W of the shard; every other slot stays zero
+                assert torch.equal(shard[slot_of[owner]].view(torch.int32),
+                                   ref_s[owner].view(torch.int32)), it
+                untouched = torch.ones_like(shard, dtype=torch.bool)
+                untouched[slot_of[owner]] = False
+                assert not shard[untouched].any(), it
+        else:
+            pairs = [(flat_m, ref_m)] + ([] if sgd else [(flat_v, ref_v)])
+            for mine_s, ref_s in pairs:
+                assert torch.equal(mine_s[owner].view(torch.int32),
+                                   ref_s[owner].view(torch.int32)), it
+                assert not mine_s[~owner].any(), it       # other ranks' chunks are never touched
     dist.barrier()
     be.comm_destroy(comm)
     del peers
@@ -368,15 +384,22 @@ def _sharded_step_worker(rank: int, world: int, port: int, out_dir: str, multica
 
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("kind", ["adamw", "sgd"])
-@pytest.mark.parametrize("path", ["p2p", "multicast"])
+@pytest.mark.parametrize("path", ["p2p", "multicast", "p2p_fullsize_moments"])
 def test_sharded_step_kernel_against_replicated_step(world, kind, path, tmp_path):
     """rk_comm_reduce_scatter_norm + rk_comm_sharded_step on awkward sizes against
     rk_comm_allreduce_norm + the ordinary step kernel: same norm, same parameters on every
-    rank, moments equal on their owners and untouched elsewhere, gradients zero-filled."""
+    rank, gradients zero-filled, moments equal to the replicated step's on their owners --
+    in the rank's compact shard (1/W of the memory; what the engine uses) or in full-size
+    per-tensor buffers -- and nothing else written."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    port = 29930 + world * 4 + 2 * (kind == "sgd") + (path == "multicast")
-    mp.spawn(_sharded_step_worker, args=(world, port, str(tmp_path), path == "multicast", kind),
+    if path == "p2p_fullsize_moments" and kind == "sgd":
+        pytest.skip("one optimizer is enough for the alternative moment layout")
+    paths = ["p2p", "multicast", "p2p_fullsize_moments"]
+    port = 29930 + world * 6 + 3 * (kind == "sgd") + paths.index(path)
+    mp.spawn(_sharded_step_worker,
+             args=(world, port, str(tmp_path), path == "multicast", kind,
+                   path != "p2p_fullsize_moments"),
              nprocs=world, join=True)
     if (tmp_path / "skipped_0").exists():
         pytest.skip("this box has no NVSwitch multicast support")

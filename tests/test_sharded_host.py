@@ -28,7 +28,7 @@ def _layout():
 
 
 def _opt_for(rank, world, params, offsets, plan):
-    opt = EngineOptimizer.__new__(EngineOptimizer)      # only the ownership helpers are used
+    opt = EngineOptimizer.__new__(EngineOptimizer)      # only the shard helpers are used
     opt.engine = SimpleNamespace(num_processes=world, process_index=rank)
     opt._params, opt._offsets = params, offsets
     opt._get_plan = lambda: plan
@@ -36,28 +36,34 @@ def _opt_for(rank, world, params, offsets, plan):
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_unowned_elements_are_zeroed_and_every_element_has_one_owner(world):
+def test_moment_shards_scatter_and_reassemble(world):
+    """Full per-parameter moments -> each rank's compact shard (1/W of the chunks) -> back.
+    Slot of chunk c on rank c % W is c // W: checked element by element against that rule."""
     params, offsets, total, plan = _layout()
+    chunk = plan.chunk_norm
     assert plan.n_chunks_norm > len(SHAPES), "the shapes must span several chunks"
-    src = torch.arange(1, total + 1, dtype=torch.float32)
-    kept = []
-    for rank in range(world):
-        flat = src.clone()
-        _opt_for(rank, world, params, offsets, plan)._zero_unowned(flat)
-        kept.append(flat)
-    for i, (p, o) in enumerate(zip(params, offsets)):
-        n = p.numel()
-        chunk_of = torch.arange(n) // plan.chunk_norm + int(plan.prefix_norm[i])
-        for rank in range(world):
-            mine = (chunk_of % world) == rank
-            seg = kept[rank][o:o + n]
-            assert torch.equal(seg[mine], src[o:o + n][mine]), (i, rank)
-            assert not seg[~mine].any(), (i, rank)
-    # what _gathered does with NCCL: integer SUM of the bit patterns rebuilds the buffer
-    bits = sum(k.view(torch.int32) for k in kept)
-    for p, o in zip(params, offsets):
-        n = p.numel()
-        assert torch.equal(bits[o:o + n], src.view(torch.int32)[o:o + n])
+    torch.manual_seed(world)
+    full = [torch.randn(p.shape) for p in params]
+    rows = -(-plan.n_chunks_norm // world)
+    shards = torch.zeros(world, rows * chunk)
+    opts = [_opt_for(r, world, params, offsets, plan) for r in range(world)]
+    for r, opt in enumerate(opts):
+        for i in range(len(params)):
+            opt._scatter(i, full[i], shards[r])
+    # the ownership rule, spelled out independently
+    used = torch.zeros(world, rows * chunk, dtype=torch.bool)
+    for i, t in enumerate(full):
+        flat = t.reshape(-1)
+        e = torch.arange(flat.numel())
+        c = e // chunk + int(plan.prefix_norm[i])
+        owner, pos = c % world, (c // world) * chunk + e % chunk
+        assert torch.equal(shards[owner, pos], flat), i
+        used[owner, pos] = True
+    assert not shards[~used].any()                        # nothing else was written
+    # and back (what _gather_chunks + _assemble do after the all-gather)
+    chunks = EngineOptimizer._interleave(shards, chunk)
+    for i, t in enumerate(full):
+        assert torch.equal(opts[0]._assemble(i, chunks), t), i
 
 
 def test_sharded_request_without_nvlink_exchange_stays_replicated():

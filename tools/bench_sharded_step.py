@@ -40,8 +40,10 @@ def main() -> None:
     g = arena[sig + scratch:sig + scratch + 4 * n].view(torch.float32)
     p = arena[sig + scratch + 4 * n:].view(torch.float32)
     p.normal_(0, 0.02)
-    m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
-    plan = be.make_plan([TensorSpec(p=p, g=g, m=m, v=v, group=0)], scratch=arena[sig:sig + scratch])
+    plan = be.make_plan([TensorSpec(p=p, g=g, m=None, v=None, group=0)],
+                        scratch=arena[sig:sig + scratch])
+    shard = -(-plan.n_chunks_norm // world) * plan.chunk_norm      # compact moment shards
+    m, v = torch.zeros(shard, device=dev), torch.zeros(shard, device=dev)
 
     class Eng:
         device, process_index, num_processes = dev, rank, world
@@ -70,7 +72,8 @@ def main() -> None:
                                             use_mc)
                 norm = be.l2norm_finalize(plan)
                 e[1].record()
-                be.comm_sharded_step(comm, plan, "adamw", table.data_ptr(), norm, 1.0, ctas, use_mc)
+                be.comm_sharded_step(comm, plan, "adamw", table.data_ptr(), norm, 1.0, ctas, use_mc,
+                                     m, v)
                 e[2].record()
                 torch.cuda.synchronize()
                 # the all-reduce form of the exchange at the same grid, for comparison
