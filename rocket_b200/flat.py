@@ -7,7 +7,8 @@ and ``.zero_grad()``, the last two being no-ops on gradient-accumulation steps.
 
 HBM layout (built once): every trainable parameter of every param group is re-homed into
 one flat fp32 buffer ``flat_p`` at a 256-byte aligned offset, and ``flat_g`` / ``flat_m`` /
-``flat_v`` mirror it.  ``param.data``, ``param.grad`` and the optimizer's
+``flat_v`` mirror it (sharded step: ``flat_p`` joins ``flat_g`` in the peer-mapped arena and
+the moments shrink to this rank's compact shards ``shard_m`` / ``shard_v``).  ``param.data``, ``param.grad`` and the optimizer's
 ``state[p]["exp_avg"]`` ... are views into those buffers, so user code, ``state_dict()`` and
 checkpoints see ordinary per-parameter tensors while the kernels see four aligned streams
 and the gradient all-reduce sees contiguous buckets (no copy-in / copy-out).
@@ -228,6 +229,8 @@ class EngineOptimizer:
 
     @property
     def state(self):
+        """torch's per-parameter state.  With a sharded step this gathers the moment shards
+        (a collective: every rank has to read it, like ``state_dict()``)."""
         self._export_state()
         return self.optimizer.state
 
@@ -272,6 +275,9 @@ class EngineOptimizer:
             return
         gp = eng.graph_pass                      # None, or a Module's CUDA-graph pass
         replay = gp is not None and gp.mode == "replay"
+        scaler = eng.scaler                      # fp16 loss scaler, or None
+        if scaler is not None and gp is not None:
+            raise NotImplementedError("Module(graph=True) with mixed_precision='fp16'")
         max_norm = self._pending_clip if self._pending_clip is not None else self.max_grad_norm
         if not replay:
             self._adopt_grads()
@@ -280,10 +286,7 @@ class EngineOptimizer:
             plan = self._get_plan()
             fused_norm = eng.finish_grad_sync(self)  # True: norm partials are in plan.scratch
             scale = self._read_scale()
-            scaler = eng.scaler
             if scaler is not None:
-                if gp is not None:
-                    raise NotImplementedError("Module(graph=True) with mixed_precision='fp16'")
                 fused_norm = False     # the exchange's partials are of the loss-scaled gradients
             norm = None
             if max_norm is not None or scaler is not None:
@@ -295,7 +298,7 @@ class EngineOptimizer:
                     norm = eng.backend.l2norm(plan, scale)
                 self.last_grad_norm = norm
         self._pending_clip = None
-        if not replay and scaler is not None:
+        if scaler is not None:
             # fp16: the norm of the unscaled gradients is also GradScaler's overflow check (any
             # non-finite element makes it non-finite); reading it is the one host sync
             # GradScaler.step makes too (found_inf.item()).  Overflow: skip the step, keep the
