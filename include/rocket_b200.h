@@ -249,8 +249,9 @@ int rk_comm_destroy(rk_comm* comm);
 /* ---- K7: sharded optimizer step -----------------------------------
  * The reference has no counterpart: under DDP every replica repeats the whole
  * torch.optim step (rocket/core/optimizer.py:129).  Here the arena additionally carries the
- * parameters   [ signal pad | norm scratch | gradients | parameters ]   and rank r owns the
- * norm chunks c with c % W == r, the same ownership as the exchange.
+ * parameters   [ signal pad | norm scratch | gradients | parameters ]   (the plan's p pointers,
+ * like its g pointers, must point into the local arena; the same offsets are used on the
+ * peers) and rank r owns the norm chunks c with c % W == r, the same ownership as the exchange.
  * rk_comm_reduce_scatter_norm is rk_comm_allreduce_norm without the broadcast half: the owner
  * alone keeps sum_r(g_r) * (1/W) of its chunks (other ranks' copies of those chunks stay as
  * they were); the norm partials still reach every rank.

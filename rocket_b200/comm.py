@@ -13,7 +13,10 @@ Two implementations share the bucketing and the hook logic:
     from all peers, scales by 1/world_size, writes the result back into every peer's buffer
     and, in the same pass, produces the sum-of-squares partials of the global gradient norm
     (so clipping needs no separate pass over the gradients).  Launched on a side stream from
-    ``post_accumulate_grad`` hooks, it overlaps the rest of backward.
+    ``post_accumulate_grad`` hooks, it overlaps the rest of backward.  With a sharded
+    optimizer step (``Optimizer(sharded=True)``, flat.py) the same kernel runs without its
+    write-back half -- a reduce-scatter: only the owner keeps the averaged chunk, updates it
+    (csrc/rk_comm.cu, rk_sharded_step_kernel) and writes the new parameters to all ranks.
 
 ``GradSync`` (NCCL; used across nodes, on CPU/gloo in tests, or with ROCKET_B200_GRAD_SYNC=nccl)
     In-place ``all_reduce(SUM)`` of each bucket on NCCL's stream; the 1/world_size factor is
