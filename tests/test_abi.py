@@ -63,3 +63,15 @@ def test_plan_host_side_is_checked_without_a_gpu():
     want = [1 - 1e-3 * 1e-2, 1e-2, 1 - 0.9, np.float32(1 - 0.9) - np.float32(1), 0.999,
             1 - 0.999, (1 - 0.999 ** 3.0) ** 0.5, 1e-8, -(1e-3 / (1 - 0.9 ** 3.0))]
     assert [np.float32(x) for x in out] == [np.float32(x) for x in want]
+
+
+def test_product_package_never_imports_the_oracle_or_the_test_double():
+    """oracle/ and tests/host_backend.py are checkers: nothing under rocket_b200/ may import,
+    load or execute them (a product path through the CPU restatement would void parity)."""
+    import re
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent / "rocket_b200"
+    pat = re.compile(r"^\s*(from|import)\s+(oracle|host_backend)\b|step_oracle|liboracle", re.M)
+    offenders = [str(p.relative_to(root)) for p in root.rglob("*")
+                 if p.suffix in (".py", ".cu", ".cuh", ".h") and pat.search(p.read_text())]
+    assert offenders == []
