@@ -511,9 +511,14 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
     be = NativeBackend(dev)
     sig = N.RK_COMM_SIGNAL_BYTES
     scratch = -(-be.scratch_bytes([n]) // 256) * 256
-    arena = alloc_arena(sig + scratch + 8 * n, dev)       # [signals | scratch | g | p]
+    # Sharded arm: hardware-validated this round at 2 and 4 GPUs (gpurun budget); at 8 it (and
+    # the parameter half of the arena it needs) is there only on request, so that the default
+    # bench line never depends on an unvalidated configuration.
+    run_sharded = world in (2, 4) or os.environ.get("ROCKET_B200_BENCH_SHARDED") == "1"
+    arena = alloc_arena(sig + scratch + (8 if run_sharded else 4) * n, dev)  # [signals|scratch|g|p]
     g = arena[sig + scratch:sig + scratch + 4 * n].view(torch.float32)
-    p = arena[sig + scratch + 4 * n:].view(torch.float32)
+    p = arena[sig + scratch + 4 * n:].view(torch.float32) if run_sharded \
+        else torch.empty(n, device=dev)
     torch.manual_seed(5)
     p.normal_(0, 0.02)
     m = torch.zeros(n, device=dev)
@@ -556,9 +561,6 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
     shard = -(-plan.n_chunks_norm // world) * plan.chunk_norm
     sm, sv = torch.zeros(shard, device=dev), torch.zeros(shard, device=dev)
     sx, ss = [], []
-    # Hardware-validated this round at 2 and 4 GPUs (gpurun budget); at 8 the arm runs only on
-    # request, so that the default bench line never depends on an unvalidated configuration.
-    run_sharded = world in (2, 4) or os.environ.get("ROCKET_B200_BENCH_SHARDED") == "1"
     for i in range(warmup + steps if run_sharded else 0):
         torch.manual_seed(1000 * i + rank)
         g.normal_(0, 1e-3)
