@@ -288,3 +288,58 @@ def test_scalar_accumulate_matches_python_double():
         be.scalar_accumulate(v.to(DEV), 3.0, acc)
         want = oracle.scalar_accumulate(want, float(v), 3.0)
     assert acc.item() == want
+
+
+@pytest.mark.parametrize("kind", ["adamw", "sgd"])
+def test_kernels_write_nothing_outside_their_tensors(kind):
+    """Bounds check with canaries (compute-sanitizer is closed on this GPU pool): every tensor
+    of an awkward-sized list sits between guard words inside one allocation per stream; after
+    the norm, the fused step (launch-argument and device-table variants) and the zero-fill,
+    every guard word must be untouched.  Odd gaps also put most tensors off the 16-byte grid,
+    so both the vectorised and the scalar paths run."""
+    from rocket_b200 import _native as N
+    from rocket_b200.backend import TensorSpec
+    be = _backend()
+    sizes = [6, 10, 150, 1, 4095, 4096, 4097, 48000, 3, 8191, 123457]
+    gaps = [5, 8, 3, 4, 7, 12, 1, 16, 9, 2, 6, 11]            # guard words before / between / after
+    total = sum(sizes) + sum(gaps)
+    sentinel = -123456.75
+    torch.manual_seed(3)
+    streams = {k: torch.full((total,), sentinel, device=DEV) for k in "pgmv"}
+    guard = torch.ones(total, dtype=torch.bool, device=DEV)
+    specs, off = [], 0
+    for i, n in enumerate(sizes):
+        off += gaps[i]
+        views = {}
+        for k, t in streams.items():
+            views[k] = t[off:off + n]
+            views[k].copy_(torch.randn(n, device=DEV) * (1e-2 if k != "v" else 1e-3))
+        views["v"].abs_()
+        guard[off:off + n] = False
+        specs.append(TensorSpec(p=views["p"], g=views["g"], m=views["m"],
+                                v=views["v"] if kind != "sgd" else None, group=i % 2))
+        off += n
+    plan = be.make_plan(specs)
+    if kind == "sgd":
+        groups = [dict(lr=0.05, momentum=0.9, dampening=0.0, weight_decay=1e-4,
+                       nesterov=gi == 1, first_step=False, skip=False) for gi in range(2)]
+        step = be.sgd_step
+    else:
+        groups = [dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01, step=3,
+                       decoupled=True, skip=False) for _ in range(2)]
+        step = be.adam_step
+    table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8, device=DEV)
+    host = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8).pin_memory()
+    norm = be.l2norm(plan, 1.0, want_tensor_norms=True)
+    step(plan, groups, norm, 1.0, 1.0, False)                  # keep g for the second variant
+    be.step_table_write(kind, groups, host)
+    table.copy_(host)
+    be.step_devtable(kind, plan, table, norm, 1.0, 1.0, True)  # ... which also zero-fills g
+    torch.cuda.synchronize()
+    touched = "pgm" if kind == "sgd" else "pgmv"
+    for k in touched:
+        assert bool((streams[k][guard] == sentinel).all()), f"guard words of stream {k} were written"
+    assert not streams["g"][~guard].any()                      # zero-fill reached every element
+    assert bool(torch.isfinite(streams["p"][~guard]).all())
+    if kind == "sgd":
+        assert bool((streams["v"][guard] == sentinel).all())
