@@ -152,3 +152,85 @@ def test_looper_port_matches_reference_golden(name):
     for k, p in got["params"].items():
         want = gold[f"param/{k}"]
         assert np.abs(p.numpy() - want).max() <= 2e-5 * np.abs(want).max(), k
+
+
+# ---- randomised pinning of the C oracle against torch's CPU kernels (hypothesis) ---------------
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+_lr = st.floats(1e-6, 1.0)
+_wd = st.sampled_from([0.0, 1e-4, 1e-2, 0.3])
+_gscale = st.sampled_from([0.0, 1e-30, 1e-8, 1e-2, 1.0, 1e4])     # incl. all-zero and huge grads
+
+
+def _grad(n, scale, seed):
+    g = torch.Generator().manual_seed(seed)
+    t = torch.randn(n, generator=g) * scale
+    t[::7] = 0.0                                  # exact zeros, as real ReLU networks produce
+    t[3::11] = 1e-42 * (1 if scale else 0)        # denormals
+    return t
+
+
+@settings(max_examples=60, deadline=None, derandomize=True)
+@given(n=st.integers(1, 3000), lr=_lr, wd=_wd, gscale=_gscale, seed=st.integers(0, 2 ** 16),
+       momentum=st.sampled_from([0.0, 0.5, 0.9, 0.99]), dampening=st.sampled_from([0.0, 0.1]),
+       nesterov=st.booleans(), steps=st.integers(1, 4))
+def test_c_oracle_sgd_random_hyperparameters_bit_exact(n, lr, wd, gscale, seed, momentum,
+                                                       dampening, nesterov, steps):
+    if nesterov and (momentum == 0.0 or dampening != 0.0):
+        nesterov = False                           # torch rejects the combination
+    torch.manual_seed(seed)
+    p = torch.nn.Parameter(torch.randn(n) * 0.05)
+    opt = torch.optim.SGD([p], lr=lr, momentum=momentum, dampening=dampening, weight_decay=wd,
+                          nesterov=nesterov, foreach=False)
+    pn = p.detach().numpy().copy()
+    buf = np.zeros(n, np.float32) if momentum else None
+    for step in range(1, steps + 1):
+        g = _grad(n, gscale, seed + step)
+        p.grad = g.clone()
+        opt.step()
+        oracle.sgd_step(pn, g.numpy().copy(), buf, lr=lr, momentum=momentum, dampening=dampening,
+                        weight_decay=wd, nesterov=nesterov, first_step=step == 1)
+        assert np.array_equal(_bits(pn), _bits(p.detach().numpy())), step
+        if momentum:
+            assert np.array_equal(_bits(buf), _bits(opt.state[p]["momentum_buffer"].numpy()))
+
+
+def _same_bits_up_to_zero_sign(a, b) -> bool:
+    """Bit equality, except that +0.0 and -0.0 count as equal.  torch's own lerp is not
+    consistent there: its vectorised body computes fmadd(w - 1, end - start, end) and its
+    scalar tail end - (end - start) * (1 - w); for w == 1 (beta1 == 0) and a gradient of -0.0
+    the first gives -0.0 and the second +0.0, so the sign of a zero moment depends on the
+    element's position in the tensor.  The oracle (and the kernels) follow the vector body."""
+    nz = (a != 0) | (b != 0)
+    return bool(np.array_equal(a, b) and np.array_equal(_bits(a)[nz], _bits(b)[nz]))
+
+
+@settings(max_examples=60, deadline=None, derandomize=True)
+@given(n=st.integers(1, 3000), lr=_lr, wd=_wd, gscale=_gscale, seed=st.integers(0, 2 ** 16),
+       beta1=st.sampled_from([0.0, 0.3, 0.5, 0.9]), beta2=st.sampled_from([0.9, 0.95, 0.999]),
+       eps=st.sampled_from([1e-8, 1e-6, 1e-3]), decoupled=st.booleans(),
+       steps=st.integers(1, 4))
+def test_c_oracle_adam_random_hyperparameters(n, lr, wd, gscale, seed, beta1, beta2, eps,
+                                              decoupled, steps):
+    """Moments bit-exact; parameters within the one sqrt ulp that separates torch's MKL sqrt
+    from the correctly rounded one (beta1 < 0.5 takes torch's other lerp branch)."""
+    torch.manual_seed(seed)
+    p = torch.nn.Parameter(torch.randn(n) * 0.05)
+    cls = torch.optim.AdamW if decoupled else torch.optim.Adam
+    opt = cls([p], lr=lr, betas=(beta1, beta2), eps=eps, weight_decay=wd, foreach=False)
+    m, v = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    for step in range(1, steps + 1):
+        g = _grad(n, gscale, seed + step)
+        p.grad = g.clone()
+        pn = p.detach().numpy().copy()            # resync every step: compare single updates
+        before = pn.copy()
+        opt.step()
+        oracle.adam_step(pn, g.numpy().copy(), m, v, lr=lr, beta1=beta1, beta2=beta2, eps=eps,
+                         weight_decay=wd, step=step, decoupled=decoupled)
+        state = opt.state[p]
+        assert _same_bits_up_to_zero_sign(m, state["exp_avg"].numpy()), step
+        assert np.array_equal(_bits(v), _bits(state["exp_avg_sq"].numpy())), step
+        want = p.detach().numpy()
+        assert np.all(np.abs(pn - want) <= 4.8e-7 * np.abs(want - before)
+                      + 2 * np.spacing(np.abs(want))), step
+        m[:] = state["exp_avg"].numpy()           # carry torch's zero signs into the next step
