@@ -343,3 +343,81 @@ def test_kernels_write_nothing_outside_their_tensors(kind):
     assert bool(torch.isfinite(streams["p"][~guard]).all())
     if kind == "sgd":
         assert bool((streams["v"][guard] == sentinel).all())
+
+
+def _draws(n, seed):
+    rng = np.random.default_rng(seed)
+    pick = lambda xs: xs[int(rng.integers(len(xs)))]        # noqa: E731
+    for _ in range(n):
+        yield dict(lr=float(10 ** rng.uniform(-6, 0)), wd=pick([0.0, 1e-4, 1e-2, 0.3]),
+                   gscale=pick([0.0, 1e-30, 1e-8, 1e-2, 1.0, 1e4]),
+                   clip=pick([None, None, 0.05, 1e3]), grad_scale=pick([1.0, 0.5, 0.125]),
+                   beta1=pick([0.0, 0.3, 0.5, 0.9, 0.99]), beta2=pick([0.9, 0.95, 0.999]),
+                   eps=pick([1e-8, 1e-6, 1e-3]), decoupled=bool(rng.integers(2)),
+                   step=int(rng.integers(1, 2000)),
+                   momentum=pick([0.0, 0.5, 0.9, 0.99]), dampening=pick([0.0, 0.1]),
+                   nesterov=bool(rng.integers(2)), first=bool(rng.integers(2)),
+                   seed=int(rng.integers(1 << 30)))
+
+
+def _refill_grads(specs, host, gscale, seed):
+    g = torch.Generator().manual_seed(seed)
+    for s, h in zip(specs, host):
+        new = torch.randn(s.g.numel(), generator=g) * gscale
+        new[::7] = 0.0                                    # dead units
+        if gscale:
+            new[3::11] = 1e-42                            # denormals
+        s.g.copy_(new)
+        h[1][:] = new.numpy()
+
+
+def test_adam_and_sgd_random_hyperparameters_bit_exact():
+    """24 seeded random draws of hyper-parameters, gradient magnitudes (all-zero to 1e4), clip
+    thresholds and 1/W factors: the fused kernels against the C oracle, every stream, bit for
+    bit (the oracle itself is pinned against torch's CPU kernels with the same kind of draws,
+    tests/test_oracle.py)."""
+    be = _backend()
+    sizes = [6, 150, 4097, 70001, 1]
+    for k, d in enumerate(_draws(24, seed=2024)):
+        # ---- Adam / AdamW
+        specs, host = _make_list(sizes, seed=d["seed"] % 1000, misalign=(1,))
+        plan = be.make_plan(specs)
+        _refill_grads(specs, host, d["gscale"], d["seed"])
+        norm = be.l2norm(plan, d["grad_scale"]) if d["clip"] is not None else None
+        hp = dict(lr=d["lr"], beta1=d["beta1"], beta2=d["beta2"], eps=d["eps"],
+                  weight_decay=d["wd"], decoupled=d["decoupled"], step=d["step"])
+        be.adam_step(plan, [hp], norm, d["clip"] or 0.0, d["grad_scale"], True)
+        torch.cuda.synchronize()
+        tn = float(norm.item()) if norm is not None else None
+        for i, (s, h) in enumerate(zip(specs, host)):
+            oracle.adam_step(h[0], h[1], h[2], h[3], lr=d["lr"], beta1=d["beta1"],
+                             beta2=d["beta2"], eps=d["eps"], weight_decay=d["wd"], step=d["step"],
+                             decoupled=d["decoupled"], grad_scale=d["grad_scale"], total_norm=tn,
+                             max_norm=d["clip"] or 0.0, zero_grads=True)
+            for name, t, a in zip("pgmv", (s.p, s.g, s.m, s.v), h):
+                got = t.cpu().numpy()
+                same = (_bits(got) == _bits(a)) | (np.isnan(got) & np.isnan(a))
+                assert same.all(), ("adam", k, d, i, name, got[~same][:4], a[~same][:4])
+        # ---- SGD
+        nesterov = d["nesterov"] and d["momentum"] != 0.0 and d["dampening"] == 0.0
+        with_m = d["momentum"] != 0.0
+        specs, host = _make_list(sizes, seed=d["seed"] % 997, misalign=(2,), with_v=False,
+                                 with_m=with_m)
+        plan = be.make_plan(specs)
+        _refill_grads(specs, host, d["gscale"], d["seed"] + 1)
+        norm = be.l2norm(plan, d["grad_scale"]) if d["clip"] is not None else None
+        hp = dict(lr=d["lr"], momentum=d["momentum"], dampening=d["dampening"],
+                  weight_decay=d["wd"], nesterov=nesterov)
+        be.sgd_step(plan, [dict(hp, first_step=d["first"])], norm, d["clip"] or 0.0,
+                    d["grad_scale"], True)
+        torch.cuda.synchronize()
+        tn = float(norm.item()) if norm is not None else None
+        for i, (s, h) in enumerate(zip(specs, host)):
+            oracle.sgd_step(h[0], h[1], h[2] if with_m else None, first_step=d["first"],
+                            grad_scale=d["grad_scale"], total_norm=tn, max_norm=d["clip"] or 0.0,
+                            zero_grads=True, **hp)
+            streams = [("p", s.p, h[0]), ("g", s.g, h[1])] + ([("m", s.m, h[2])] if with_m else [])
+            for name, t, a in streams:
+                got = t.cpu().numpy()
+                same = (_bits(got) == _bits(a)) | (np.isnan(got) & np.isnan(a))
+                assert same.all(), ("sgd", k, d, i, name, got[~same][:4], a[~same][:4])
