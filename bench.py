@@ -31,7 +31,6 @@ import statistics
 import subprocess
 import sys
 import threading
-import time
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
@@ -124,7 +123,6 @@ def make_resnet50():
 # The default is the driver's headline workload (configs[1]).  `resnet50` is configs[2]
 # (ImageNet-shaped, bf16 autocast, SGD momentum) for the 1 -> 8 GPU scaling target.
 def make_gpt2():
-    import torch.nn.functional as F
     from transformers import GPT2Config, GPT2LMHeadModel
     torch.manual_seed(0)
     lm = GPT2LMHeadModel(GPT2Config(resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0))

@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import ctypes
 from ctypes import (POINTER, Structure, c_char_p, c_double, c_float, c_int, c_int32, c_int64,
-                    c_longlong, c_size_t, c_uint64, c_void_p)
+                    c_size_t, c_uint64, c_void_p)
 from pathlib import Path
 
 LIB_PATH = Path(__file__).resolve().parent / "csrc" / "librocket_b200.so"

@@ -1,6 +1,6 @@
 """Microbench (N GPUs, torchrun): fused NVLink all-reduce+norm kernel vs NCCL all_reduce + norm kernel
 over a flat gradient buffer of n fp32 elements.  Prints per-rank-max times and bus bandwidth."""
-import os, sys, time
+import os, sys
 from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))

@@ -19,7 +19,6 @@ def wrap(cls, name="launch"):
 for c in (rk.Dataset, rk.Module, rk.Loss, rk.Optimizer):
     wrap(c)
 from rocket_b200 import staging
-from rocket_b200.utils import torch as rt
 wrap2 = lambda cls, name: (lambda orig: setattr(cls, name, (lambda self, *a, **k: _t(cls.__name__ + "." + name, orig, self, *a, **k))))(getattr(cls, name))
 def _t(key, orig, *a, **k):
     t = time.perf_counter(); r = orig(*a, **k); acc[key] += time.perf_counter() - t; cnt[key] += 1; return r
