@@ -193,6 +193,11 @@ def run_ours(args) -> dict:
     W, K = args.warmup, args.steps
     TAIL = 8 if args.graph else 0      # synchronised replays after the timed region (kernel timing)
     assert W >= 3, "timing rules: at least 3 warm-up steps"
+    if args.graph:
+        # Module(graph=True) runs GRAPH_WARMUP eager iterations per input signature and then
+        # captures: with a short --warmup the capture would land inside the timed region.
+        # Extra untimed steps keep it out; the line reports the warm-up actually done.
+        W = max(W, (rk.Module.GRAPH_WARMUP + 2) * WL.get("accum", 1))
     torch.backends.cudnn.benchmark = True
 
     class TimedBackend(NativeBackend):
