@@ -184,6 +184,14 @@ int rk_sgd_step_multi(const void* plan_host, const void* plan_dev,
                       const float* total_norm_dev, float max_norm,
                       float grad_scale, int zero_grads, void* stream);
 
+/* Tuning hook (no counterpart in the reference): K2/K3 exist in several code shapes --
+ * per-thread 128-bit or 256-bit ld/st.global walkers at different occupancies, and a
+ * bulk-copy (cp.async.bulk + mbarrier ring) kernel -- all running the same element code,
+ * hence the same bits.  The library picks one by list size; `variant >= 0` forces one
+ * process-wide (the numbers are listed beside the switch in csrc/rk_step.cu), `-1` restores
+ * the automatic choice.  Environment RK_STEP_VARIANT sets the initial value.             */
+int rk_step_variant_override(int variant);
+
 /* ---- K2/K3 with the per-group constants in device memory ---------------------------------
  * For CUDA-graph replays, where kernel arguments are frozen at capture: rk_*_table_write
  * derives the same per-group constants as the calls above into RK_STEP_TABLE_BYTES of

@@ -15,7 +15,7 @@ from pathlib import Path
 CSRC = Path(__file__).resolve().parent / "csrc"
 LIB_PATH = CSRC / "librocket_b200.so"
 SOURCES = ["rk_api.cu", "rk_norm.cu", "rk_step.cu", "rk_meter.cu", "rk_stage.cu", "rk_comm.cu"]
-HEADERS = [CSRC / "rk_common.cuh", CSRC / "rk_step_ops.cuh", CSRC.parent.parent / "include" / "rocket_b200.h"]
+HEADERS = [CSRC / "rk_common.cuh", CSRC / "rk_step_ops.cuh", CSRC / "rk_step_bulk.cuh", CSRC.parent.parent / "include" / "rocket_b200.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

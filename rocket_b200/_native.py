@@ -27,7 +27,7 @@ EXPORTS = [
     "rk_stage_wait", "rk_stage_release", "rk_stage_destroy", "rk_l2norm_finalize",
     "rk_comm_create", "rk_comm_allreduce_norm", "rk_comm_destroy", "rk_adam_table_write",
     "rk_sgd_table_write", "rk_adamw_step_multi_devtable", "rk_sgd_step_multi_devtable",
-    "rk_comm_reduce_scatter_norm", "rk_comm_sharded_step",
+    "rk_comm_reduce_scatter_norm", "rk_comm_sharded_step", "rk_step_variant_override",
 ]
 
 
@@ -103,6 +103,7 @@ def load() -> ctypes.CDLL:
                                                  c_float, c_int, c_void_p]
     lib.rk_sgd_step_multi_devtable.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_float,
                                                c_float, c_int, c_void_p]
+    lib.rk_step_variant_override.argtypes = [c_int]
     for name in EXPORTS:
         fn = getattr(lib, name)          # AttributeError here = header/library mismatch
         if name not in ("rk_last_error", "rk_launch_count"):

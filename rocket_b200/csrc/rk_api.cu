@@ -159,6 +159,7 @@ extern "C" int rk_plan_build(const rk_tensor_desc* descs, int n_tensors, void* p
     d[i].flags &= RK_TENSOR_SKIP;
     uintptr_t bits = (uintptr_t)s.p | (uintptr_t)s.g | (uintptr_t)s.m | (uintptr_t)s.v;
     if ((bits & 15) == 0) d[i].flags |= RK_TENSOR_VEC4;
+    if ((bits & 31) == 0) d[i].flags |= RK_TENSOR_VEC8;
     ps[i] = cs;
     pn[i] = cn;
     cs += (int32_t)((s.numel + L.h.chunk_step - 1) / L.h.chunk_step);

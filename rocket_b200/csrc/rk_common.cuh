@@ -62,6 +62,8 @@ struct rk_plan_header {
 
 // Tensors whose four pointers are 16-byte aligned take the 128-bit path.
 #define RK_TENSOR_VEC4 (1 << 8)
+// ... 32-byte aligned: the 256-bit path.
+#define RK_TENSOR_VEC8 (1 << 9)
 
 // How many prefix entries a CTA stages in shared memory; longer lists are searched
 // in global memory (L1/L2 resident).

@@ -15,6 +15,8 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "rk_common.cuh"
 
 #define STEP_THREADS 256
@@ -118,6 +120,94 @@ rk_step_kernel(const char* __restrict__ plan, const __grid_constant__ Table tabl
   }
 }
 
+
+// ---- 256-bit variant ---------------------------------------------------------------------
+// Same walker with ld.global.v8 / st.global.v8 (LDG.256 / STG.256): half the memory
+// instructions per byte.  Tensors whose pointers are not 32-byte aligned take the scalar path.
+template <class Op, class Table, int U, int MINB>
+__global__ void __launch_bounds__(STEP_THREADS, MINB)
+rk_step_kernel_v8(const char* __restrict__ plan, const __grid_constant__ Table table,
+                  const Table* __restrict__ dtable, const float* __restrict__ total_norm,
+                  float max_norm, float grad_scale, int zero_grads) {
+  __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
+  const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
+  const int n_tensors = h->n_tensors;
+  const int n_chunks = h->n_chunks_step;
+  const int chunk = h->chunk_step;
+  const rk_tensor_desc* descs = reinterpret_cast<const rk_tensor_desc*>(plan + h->off_descs);
+  const int32_t* prefix = rk_stage_prefix(
+      reinterpret_cast<const int32_t*>(plan + h->off_prefix_step), n_tensors + 1, s_prefix);
+  Prolog pr;
+  pr.scale = grad_scale;
+  pr.has_scale = grad_scale != 1.0f;
+  pr.has_clip = total_norm != nullptr;
+  pr.coef = pr.has_clip ? rk_clip_coef(__ldg(total_norm), max_norm) : 1.0f;
+  const int tid = threadIdx.x;
+  float8 z8;
+  z8.lo = z8.hi = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+    const int t = rk_find_tensor(prefix, n_tensors, c);
+    const rk_tensor_desc d = descs[t];
+    Op op;
+    op.h = dtable ? dtable->g[d.group] : table.g[d.group];
+    if ((d.flags & RK_TENSOR_SKIP) || (op.h.flags & GROUP_SKIP)) continue;
+    const int64_t base = (int64_t)(c - prefix[t]) * chunk;
+    const int64_t rem = d.numel - base;
+    const int count = rem < chunk ? (int)rem : chunk;
+    float* P = d.p + base;
+    float* G = d.g + base;
+    float* M = d.m + base;
+    float* V = Op::kHasV ? d.v + base : nullptr;
+    const bool has_m = d.m != nullptr;
+    int done = 0;
+    if (d.flags & RK_TENSOR_VEC8) {
+      const int nvec = count >> 3;
+      for (int i0 = tid; i0 < nvec; i0 += STEP_THREADS * U) {
+        float8 p8[U], g8[U], m8[U], v8[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+          const int i = i0 + k * STEP_THREADS;
+          if (i < nvec) {
+            p8[k] = ldg8(P + 8 * i);
+            g8[k] = ldg8(G + 8 * i);
+            if (has_m) m8[k] = ldg8(M + 8 * i);
+            if (Op::kHasV) v8[k] = ldg8(V + 8 * i);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+          const int i = i0 + k * STEP_THREADS;
+          if (i < nvec) {
+            op(p8[k].lo.x, prolog_g(g8[k].lo.x, pr), m8[k].lo.x, v8[k].lo.x);
+            op(p8[k].lo.y, prolog_g(g8[k].lo.y, pr), m8[k].lo.y, v8[k].lo.y);
+            op(p8[k].lo.z, prolog_g(g8[k].lo.z, pr), m8[k].lo.z, v8[k].lo.z);
+            op(p8[k].lo.w, prolog_g(g8[k].lo.w, pr), m8[k].lo.w, v8[k].lo.w);
+            op(p8[k].hi.x, prolog_g(g8[k].hi.x, pr), m8[k].hi.x, v8[k].hi.x);
+            op(p8[k].hi.y, prolog_g(g8[k].hi.y, pr), m8[k].hi.y, v8[k].hi.y);
+            op(p8[k].hi.z, prolog_g(g8[k].hi.z, pr), m8[k].hi.z, v8[k].hi.z);
+            op(p8[k].hi.w, prolog_g(g8[k].hi.w, pr), m8[k].hi.w, v8[k].hi.w);
+            stg8(P + 8 * i, p8[k]);
+            if (has_m) stg8(M + 8 * i, m8[k]);
+            if (Op::kHasV) stg8(V + 8 * i, v8[k]);
+            if (zero_grads) stg8(G + 8 * i, z8);
+          }
+        }
+      }
+      done = nvec << 3;      // < 8 leftover elements
+    }
+    for (int i = done + tid; i < count; i += STEP_THREADS) {
+      float p = ldg1(P + i), m = has_m ? ldg1(M + i) : 0.f, v = Op::kHasV ? ldg1(V + i) : 0.f;
+      op(p, prolog_g(ldg1(G + i), pr), m, v);
+      stg1(P + i, p);
+      if (has_m) stg1(M + i, m);
+      if (Op::kHasV) stg1(V + i, v);
+      if (zero_grads) stg1(G + i, 0.f);
+    }
+  }
+}
+
+#include "rk_step_bulk.cuh"
+
 // ---- host side ---------------------------------------------------------------------------
 static inline bool need_m(const AdamDev&) { return true; }
 static inline bool need_m(const SgdDev& g) { return (g.flags & SGD_HAS_MOM) != 0; }
@@ -135,6 +225,56 @@ static int launch_variant(const rk_plan_header* h, const void* plan_dev, const T
   return 0;
 }
 
+
+template <class Op, class Table, int U, int MINB>
+static int launch_v8(const rk_plan_header* h, const void* plan_dev, const Table& table,
+                     const Table* dtable, const float* total_norm_dev, float max_norm,
+                     float grad_scale, int zero_grads, void* stream) {
+  auto kernel = rk_step_kernel_v8<Op, Table, U, MINB>;
+  int grid = 0;
+  int rc = rk_persistent_grid((const void*)kernel, STEP_THREADS, 0, h->n_chunks_step, &grid);
+  if (rc) return rc;
+  kernel<<<grid, STEP_THREADS, 0, (cudaStream_t)stream>>>(
+      (const char*)plan_dev, table, dtable, total_norm_dev, max_norm, grad_scale, zero_grads);
+  return 0;
+}
+
+// Bulk-copy kernel: one CTA per SM, ring of `stages` tiles of `tile` elements x 4 streams.
+template <class Op, class Table, int CW>
+static int launch_bulk(const rk_plan_header* h, const void* plan_dev, const Table& table,
+                       const Table* dtable, const float* total_norm_dev, float max_norm,
+                       float grad_scale, int zero_grads, void* stream, int tile_req) {
+  auto kernel = rk_step_bulk_kernel<Op, Table, CW>;
+  int tile = tile_req < h->chunk_step ? tile_req : h->chunk_step;
+  RK_REQUIRE(tile >= 256 && h->chunk_step % tile == 0, RK_ERR_INVALID,
+             "bulk step: tile %d does not divide the step chunk %d", tile, h->chunk_step);
+  int stages = BULK_SMEM_DATA / (tile * 16);
+  if (stages > BULK_MAX_STAGES) stages = BULK_MAX_STAGES;
+  const size_t dyn = (size_t)stages * tile * 16;
+  static std::mutex mu;
+  static bool configured[64];
+  int dev = 0;
+  RK_CUDA(cudaGetDevice(&dev));
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (dev < 64 && !configured[dev]) {
+      RK_CUDA(cudaFuncSetAttribute((const void*)kernel,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   BULK_SMEM_DATA));
+      configured[dev] = true;
+    }
+  }
+  const long long items = (long long)h->n_chunks_step * (h->chunk_step / tile);
+  int grid = 0;
+  int rc = rk_persistent_grid((const void*)kernel, 32 * (CW + 1), BULK_SMEM_DATA,
+                              items > INT32_MAX ? INT32_MAX : (int)items, &grid);
+  if (rc) return rc;
+  kernel<<<grid, 32 * (CW + 1), dyn, (cudaStream_t)stream>>>(
+      (const char*)plan_dev, table, dtable, total_norm_dev, max_norm, grad_scale, zero_grads,
+      tile, stages);
+  return 0;
+}
+
 // Tuning variants (selected with RK_STEP_VARIANT while measuring; the default is the one
 // the ncu captures under profiles/ justify).
 #ifndef RK_STEP_DEFAULT_VARIANT
@@ -146,11 +286,19 @@ static int launch_variant(const rk_plan_header* h, const void* plan_dev, const T
 // Lists that fit a few waves (a ResNet-18: 11M parameters, ~75 us) are latency- and
 // tail-bound: one load per stream in flight and twice the resident CTAs wins there
 // (66.5 us vs 76.2 us in the ResNet-18 step), while 2^26+ elements want U=2 / 3 CTAs per SM.
+static std::atomic<int> g_step_variant{-2};   // -2: not read yet, -1: automatic
+
+extern "C" int rk_step_variant_override(int variant) {
+  g_step_variant.store(variant < 0 ? -1 : variant);
+  return 0;
+}
+
 static int step_variant(const rk_plan_header* h) {
-  static int forced = -2;
+  int forced = g_step_variant.load();
   if (forced == -2) {
     const char* e = getenv("RK_STEP_VARIANT");
     forced = e ? atoi(e) : -1;
+    g_step_variant.store(forced);
   }
   if (forced >= 0) return forced;
   return h->total_numel >= ((int64_t)1 << 26) ? RK_STEP_DEFAULT_VARIANT : RK_STEP_SMALL_VARIANT;
@@ -189,6 +337,23 @@ static int launch_step(const void* plan_host, const void* plan_dev, const Table&
     case 1: RK_V(2, 4, 0); break;
     case 2: RK_V(1, 6, 0); break;
     case 12: RK_V(2, 3, 2); break;  // streaming (evict-first) loads and stores
+#define RK_V8(U, MINB)                                                                     \
+  rc = launch_v8<Op, Table, U, MINB>(h, plan_dev, table, dtable, total_norm_dev, max_norm, \
+                                     grad_scale, zero_grads, stream)
+    case 30: RK_V8(1, 3); break;    // 256-bit accesses, same bytes in flight as variant 4
+    case 31: RK_V8(1, 4); break;
+    case 32: RK_V8(2, 2); break;
+    case 33: RK_V8(1, 5); break;
+#undef RK_V8
+#define RK_VB(CW, TILE)                                                                      \
+  rc = launch_bulk<Op, Table, CW>(h, plan_dev, table, dtable, total_norm_dev, max_norm,      \
+                                  grad_scale, zero_grads, stream, TILE)
+    case 20: RK_VB(16, 2048); break;  // bulk-copy ring: 6 stages x 32 KB, 16 compute warps
+    case 21: RK_VB(16, 4096); break;  // 3 stages x 64 KB
+    case 22: RK_VB(8, 2048); break;
+    case 23: RK_VB(16, 1024); break;  // 12 stages x 16 KB
+    case 24: RK_VB(8, 1024); break;
+#undef RK_VB
   }
 #undef RK_V
   if (rc) return rc;
