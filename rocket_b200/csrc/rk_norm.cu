@@ -14,6 +14,7 @@
 #define NORM_WARPS (NORM_THREADS / 32)
 #define NORM_UNROLL 4
 #define NORM_BIG_TENSOR 1024  // tensors with more chunks than this are reduced block-wide
+#define NORM_THREAD_TENSOR 8  // tensors with at most this many chunks are summed by one thread
 
 __device__ __forceinline__ float sq_acc(float acc, float x, float s) {
   float y = x * s;
@@ -21,20 +22,42 @@ __device__ __forceinline__ float sq_acc(float acc, float x, float s) {
 }
 
 // ---- level 2: partials -> per-tensor norms -> total norm, by ONE CTA, in a fixed order ----
+// `gprefix`: the norm-chunk prefix table, in shared memory whenever the caller could stage it
+// (a global-memory table costs one L2 round trip per tensor in loops that branch on it: that
+// was 15 of the 27 us this kernel took on a ResNet-18, profiles/r2_norm_notes.md).
 __device__ __forceinline__ void rk_norm_level2(const rk_plan_header* h,
-                                               const int32_t* __restrict__ gprefix,
+                                               const int32_t* gprefix,
                                                const double* partials, float* tnorms,
                                                char* scratch, float* total_out,
                                                float* tnorm_out, unsigned int* ticket,
                                                double (*s_red)[NORM_WARPS]) {
   const int n_tensors = h->n_tensors;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  // ---- level 2a: per-tensor norms, one warp per small tensor -----------------------
-  for (int t = warp; t < n_tensors; t += NORM_WARPS) {
+  // ---- level 2a: per-tensor norms ---------------------------------------------------
+  // Tensors of at most NORM_THREAD_TENSOR chunks: one THREAD each, summing its partials in
+  // chunk order, four loads in flight.  A list is mostly such tensors (biases, norms, small
+  // matrices), and one warp per tensor made this loop a chain of per-tensor round trips: 186 us
+  // for the 1185 tensors of the configs[4] list (tools/diag_norm_split.py).
+  int any_big = 0, any_mid = 0;
+  for (int t = tid; t < n_tensors; t += NORM_THREADS) {
     const int c0 = gprefix[t], c1 = gprefix[t + 1];
-    if (c1 - c0 > NORM_BIG_TENSOR) continue;
-    // four independent accumulators: four L2 loads in flight per lane (this loop is the
-    // serial tail of the kernel on small models)
+    if (c1 - c0 > NORM_THREAD_TENSOR) { any_mid = 1; continue; }
+    double s = 0.0;
+    int c = c0;
+    for (; c + 3 < c1; c += 4) {
+      const double x0 = __ldcg(partials + c), x1 = __ldcg(partials + c + 1);
+      const double x2 = __ldcg(partials + c + 2), x3 = __ldcg(partials + c + 3);
+      s += x0; s += x1; s += x2; s += x3;
+    }
+    for (; c < c1; ++c) s += __ldcg(partials + c);
+    tnorms[t] = (float)sqrt(s);
+  }
+  // ... up to NORM_BIG_TENSOR chunks: one warp each
+  any_mid = __syncthreads_or(any_mid);
+  for (int t = warp; any_mid && t < n_tensors; t += NORM_WARPS) {
+    const int c0 = gprefix[t], c1 = gprefix[t + 1];
+    if (c1 - c0 <= NORM_THREAD_TENSOR) continue;
+    if (c1 - c0 > NORM_BIG_TENSOR) { any_big = 1; continue; }
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
     int c = c0 + lane;
     for (; c + 96 < c1; c += 128) {
@@ -49,7 +72,8 @@ __device__ __forceinline__ void rk_norm_level2(const rk_plan_header* h,
   }
   // ---- level 2b: big tensors, whole CTA each ---------------------------------------
   int par = 0;
-  for (int t = 0; t < n_tensors; ++t) {
+  any_big = __syncthreads_or(any_big);
+  for (int t = 0; any_big && t < n_tensors; ++t) {
     const int c0 = gprefix[t], c1 = gprefix[t + 1];
     if (c1 - c0 <= NORM_BIG_TENSOR) continue;
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
@@ -94,12 +118,17 @@ __device__ __forceinline__ void rk_norm_level2(const rk_plan_header* h,
   }
 }
 
-__global__ void __launch_bounds__(NORM_THREADS)
+// 8 resident CTAs per SM (32 registers): the level-1 loop keeps one batch of loads per CTA in
+// flight, so bytes in flight scale with residency (6 CTAs: 6.2 TB/s, 5 CTAs: 5.1 TB/s at 1e9).
+__global__ void __launch_bounds__(NORM_THREADS, 8)
 rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restrict__ scratch,
                  float* __restrict__ total_out, float* __restrict__ tnorm_out) {
   __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   __shared__ double s_red[2][NORM_WARPS];
   __shared__ int s_last;
+  // a step kernel launched as a programmatic dependent may set itself up (and prefetch) while
+  // this kernel runs; it reads the norm only behind its griddepcontrol.wait
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
   const int n_tensors = h->n_tensors;
@@ -115,29 +144,52 @@ rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restri
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool stream_loads = h->total_numel > ((int64_t)16 << 20);   // > 64 MB of gradients
 
+  // Which tensor a chunk belongs to, where it starts and how long it is.  The lookup for the
+  // CTA's next chunk (binary search in shared memory + one descriptor read from L2) is issued
+  // while the current chunk's loads are in flight, so it costs no time between chunks.
+  struct Chunk { const float* g; int count; };
+  auto lookup = [&](int c) {
+    Chunk w;
+    w.g = nullptr;
+    w.count = 0;
+    if (c < n_chunks) {
+      const int t = rk_find_tensor(prefix, n_tensors, c);
+      const int64_t base = (int64_t)(c - prefix[t]) * chunk;
+      const int64_t rem = descs[t].numel - base;
+      w.count = rem < chunk ? (int)rem : chunk;
+      w.g = (descs[t].flags & RK_TENSOR_SKIP) ? nullptr : descs[t].g + base;
+    }
+    return w;
+  };
+  auto load_batch = [&](const float4* __restrict__ g4, int i, int nvec, float4 (&x)[NORM_UNROLL]) {
+#pragma unroll
+    for (int k = 0; k < NORM_UNROLL; ++k) {
+      const int idx = i + k * NORM_THREADS;
+      // lists that fit in L2 are read again by the step kernel right away: keep them
+      // cached; larger ones are streamed (evict-first) so they do not thrash L2
+      x[k] = idx >= nvec ? make_float4(0.f, 0.f, 0.f, 0.f)
+                         : (stream_loads ? __ldcs(g4 + idx) : __ldg(g4 + idx));
+    }
+  };
+
   int parity = 0;
+  Chunk cur = lookup(blockIdx.x);
   for (int c = blockIdx.x; c < n_chunks; c += gridDim.x, parity ^= 1) {
-    const int t = rk_find_tensor(prefix, n_tensors, c);
-    const int64_t numel = descs[t].numel;
-    const int flags = descs[t].flags;
-    const int64_t base = (int64_t)(c - prefix[t]) * chunk;
-    const int64_t rem = numel - base;
-    const int count = rem < chunk ? (int)rem : chunk;
+    Chunk nxt;
+    bool have_next = false;
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    if (!(flags & RK_TENSOR_SKIP)) {
-      const float* __restrict__ g = descs[t].g + base;
+    if (cur.g != nullptr) {
+      const float* __restrict__ g = cur.g;
+      const int count = cur.count;
       if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
         const float4* __restrict__ g4 = reinterpret_cast<const float4*>(g);
         const int nvec = count >> 2;
         for (int i = tid; i < nvec; i += NORM_THREADS * NORM_UNROLL) {
           float4 x[NORM_UNROLL];
-#pragma unroll
-          for (int k = 0; k < NORM_UNROLL; ++k) {
-            const int idx = i + k * NORM_THREADS;
-            // lists that fit in L2 are read again by the step kernel right away: keep them
-            // cached; larger ones are streamed (evict-first) so they do not thrash L2
-            x[k] = idx >= nvec ? make_float4(0.f, 0.f, 0.f, 0.f)
-                               : (stream_loads ? __ldcs(g4 + idx) : __ldg(g4 + idx));
+          load_batch(g4, i, nvec, x);
+          if (!have_next) {                 // behind the first batch of loads
+            nxt = lookup(c + gridDim.x);
+            have_next = true;
           }
 #pragma unroll
           for (int k = 0; k < NORM_UNROLL; ++k) {
@@ -153,6 +205,8 @@ rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restri
         for (int i = tid; i < count; i += NORM_THREADS) a0 = sq_acc(a0, g[i], grad_scale);
       }
     }
+    if (!have_next) nxt = lookup(c + gridDim.x);
+    cur = nxt;
     double s = (double)a0 + (double)a1 + ((double)a2 + (double)a3);
     s = rk_warp_sum(s);
     if (lane == 0) s_red[parity][warp] = s;
@@ -175,7 +229,7 @@ rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restri
   if (!s_last) return;
   __threadfence();
 
-  rk_norm_level2(h, gprefix, partials, tnorms, scratch, total_out, tnorm_out, ticket, s_red);
+  rk_norm_level2(h, prefix, partials, tnorms, scratch, total_out, tnorm_out, ticket, s_red);
 }
 
 // Level 2 on its own: for partials produced elsewhere (the fused all-reduce kernel writes
@@ -183,9 +237,12 @@ rk_l2norm_kernel(const char* __restrict__ plan, float grad_scale, char* __restri
 __global__ void __launch_bounds__(NORM_THREADS)
 rk_l2norm_finalize_kernel(const char* __restrict__ plan, char* __restrict__ scratch,
                           float* __restrict__ total_out, float* __restrict__ tnorm_out) {
+  __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   __shared__ double s_red[2][NORM_WARPS];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
-  const int32_t* gprefix = reinterpret_cast<const int32_t*>(plan + h->off_prefix_norm);
+  const int32_t* gprefix = rk_stage_prefix(
+      reinterpret_cast<const int32_t*>(plan + h->off_prefix_norm), h->n_tensors + 1, s_prefix);
   rk_norm_level2(h, gprefix, reinterpret_cast<const double*>(scratch + h->off_partials),
                  reinterpret_cast<float*>(scratch + h->off_tnorms), scratch, total_out,
                  tnorm_out, reinterpret_cast<unsigned int*>(scratch + h->off_ticket), s_red);

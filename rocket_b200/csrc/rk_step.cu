@@ -240,14 +240,18 @@ static int launch_v8(const rk_plan_header* h, const void* plan_dev, const Table&
 }
 
 // Bulk-copy kernel: one CTA per SM, ring of `stages` tiles of `tile` elements x 4 streams.
+// pdl: launch with programmatic stream serialization, so that the kernel's set-up and first
+// loads overlap the tail of the norm kernel in front of it (see grid_dependency_wait()).
 template <class Op, class Table, int CW>
 static int launch_bulk(const rk_plan_header* h, const void* plan_dev, const Table& table,
                        const Table* dtable, const float* total_norm_dev, float max_norm,
-                       float grad_scale, int zero_grads, void* stream, int tile_req) {
+                       float grad_scale, int zero_grads, void* stream, int tile, bool pdl) {
   auto kernel = rk_step_bulk_kernel<Op, Table, CW>;
-  int tile = tile_req < h->chunk_step ? tile_req : h->chunk_step;
-  RK_REQUIRE(tile >= 256 && h->chunk_step % tile == 0, RK_ERR_INVALID,
-             "bulk step: tile %d does not divide the step chunk %d", tile, h->chunk_step);
+  RK_REQUIRE(tile >= 256 && tile <= RK_NORM_CHUNK_MIN && (tile & (tile - 1)) == 0,
+             RK_ERR_INVALID, "bulk step: tile %d is not a power of two in [256, %d]", tile,
+             RK_NORM_CHUNK_MIN);
+  int tile_log2 = 0;
+  while ((1 << tile_log2) < tile) ++tile_log2;
   int stages = BULK_SMEM_DATA / (tile * 16);
   if (stages > BULK_MAX_STAGES) stages = BULK_MAX_STAGES;
   const size_t dyn = (size_t)stages * tile * 16;
@@ -264,24 +268,35 @@ static int launch_bulk(const rk_plan_header* h, const void* plan_dev, const Tabl
       configured[dev] = true;
     }
   }
-  const long long items = (long long)h->n_chunks_step * (h->chunk_step / tile);
+  const long long items = (long long)h->n_chunks_norm * (h->chunk_norm / tile);
+  RK_REQUIRE(items < (long long)INT32_MAX, RK_ERR_TOO_LARGE,
+             "bulk step: %lld tiles exceed int32", items);
   int grid = 0;
-  int rc = rk_persistent_grid((const void*)kernel, 32 * (CW + 1), BULK_SMEM_DATA,
-                              items > INT32_MAX ? INT32_MAX : (int)items, &grid);
+  int rc = rk_persistent_grid((const void*)kernel, 32 * (CW + 1), BULK_SMEM_DATA, (int)items,
+                              &grid);
   if (rc) return rc;
-  kernel<<<grid, 32 * (CW + 1), dyn, (cudaStream_t)stream>>>(
-      (const char*)plan_dev, table, dtable, total_norm_dev, max_norm, grad_scale, zero_grads,
-      tile, stages);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(32 * (CW + 1));
+  cfg.dynamicSmemBytes = dyn;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  RK_CUDA(cudaLaunchKernelEx(&cfg, kernel, (const char*)plan_dev, table, dtable, total_norm_dev,
+                             max_norm, grad_scale, zero_grads, tile_log2, stages));
   return 0;
 }
 
 // Tuning variants (selected with RK_STEP_VARIANT while measuring; the default is the one
 // the ncu captures under profiles/ justify).
 #ifndef RK_STEP_DEFAULT_VARIANT
-#define RK_STEP_DEFAULT_VARIANT 4
+#define RK_STEP_DEFAULT_VARIANT 21
 #endif
 #ifndef RK_STEP_SMALL_VARIANT
-#define RK_STEP_SMALL_VARIANT 9
+#define RK_STEP_SMALL_VARIANT 21
 #endif
 // Lists that fit a few waves (a ResNet-18: 11M parameters, ~75 us) are latency- and
 // tail-bound: one load per stream in flight and twice the resident CTAs wins there
@@ -345,14 +360,15 @@ static int launch_step(const void* plan_host, const void* plan_dev, const Table&
     case 32: RK_V8(2, 2); break;
     case 33: RK_V8(1, 5); break;
 #undef RK_V8
-#define RK_VB(CW, TILE)                                                                      \
+#define RK_VB(CW, TILE, PDL)                                                                 \
   rc = launch_bulk<Op, Table, CW>(h, plan_dev, table, dtable, total_norm_dev, max_norm,      \
-                                  grad_scale, zero_grads, stream, TILE)
-    case 20: RK_VB(16, 2048); break;  // bulk-copy ring: 6 stages x 32 KB, 16 compute warps
-    case 21: RK_VB(16, 4096); break;  // 3 stages x 64 KB
-    case 22: RK_VB(8, 2048); break;
-    case 23: RK_VB(16, 1024); break;  // 12 stages x 16 KB
-    case 24: RK_VB(8, 1024); break;
+                                  grad_scale, zero_grads, stream, TILE, PDL)
+    case 21: RK_VB(16, 4096, true); break;   // bulk-copy ring: 3 stages x 64 KB, 16 compute warps
+    case 20: RK_VB(16, 2048, true); break;   // 6 stages x 32 KB
+    case 22: RK_VB(16, 1024, true); break;   // 12 stages x 16 KB
+    case 23: RK_VB(12, 4096, true); break;
+    case 24: RK_VB(8, 4096, true); break;
+    case 25: RK_VB(16, 4096, false); break;  // as 21, ordinary stream-ordered launch
 #undef RK_VB
   }
 #undef RK_V

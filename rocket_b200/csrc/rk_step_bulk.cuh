@@ -85,29 +85,44 @@ __device__ __forceinline__ void fence_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
-// CW consumer warps + 1 producer warp.  `tile` elements per stage and stream (a divisor of the
-// plan's step chunk, or the chunk itself), `stages` ring slots; both chosen by the host.
+// Programmatic dependent launch: when this kernel is launched with the programmatic-stream-
+// serialization attribute right behind a kernel that triggers early (the norm kernels do), its
+// CTAs may start while that kernel is still finishing.  Everything that depends on the
+// previous kernel's output (the norm) or overwrites what it reads (the gradients) comes after
+// this wait; the producer's first bulk loads do not, and overlap the previous kernel's tail.
+__device__ __forceinline__ void grid_dependency_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+// CW consumer warps + 1 producer warp.  `tile_log2`: elements per stage and stream (a power of
+// two <= 4096, so it divides the plan's norm chunk), `stages` ring slots; chosen by the host.
 template <class Op, class Table, int CW>
 __global__ void __launch_bounds__(32 * (CW + 1), 1)
 rk_step_bulk_kernel(const char* __restrict__ plan, const __grid_constant__ Table table,
                     const Table* __restrict__ dtable, const float* __restrict__ total_norm,
-                    float max_norm, float grad_scale, int zero_grads, int tile, int stages) {
+                    float max_norm, float grad_scale, int zero_grads, int tile_log2,
+                    int stages) {
   extern __shared__ __align__(128) unsigned char s_ring[];
   __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   __shared__ __align__(8) uint64_t s_full[BULK_MAX_STAGES];
   __shared__ __align__(8) uint64_t s_done[BULK_MAX_STAGES];
   __shared__ BulkItem s_item[BULK_MAX_STAGES];
 
+  // Work items are tiles of the NORM chunking (chunks of >= 4096 elements, cut into `tile`
+  // element pieces): large enough that the per-tile hand-off between producer and consumers
+  // is amortised, whatever the step chunking of the LDG kernels is.
   const rk_plan_header* h = reinterpret_cast<const rk_plan_header*>(plan);
   const int n_tensors = h->n_tensors;
-  const int chunk = h->chunk_step;
-  const int tiles_per_chunk = chunk / tile;
-  const long long n_items = (long long)h->n_chunks_step * tiles_per_chunk;
+  const int tile = 1 << tile_log2;
+  const int chunk = h->chunk_norm;
+  const int sub_log2 = __ffs(chunk) - 1 - tile_log2;     // log2(tiles per chunk)
+  const int sub_mask = (1 << sub_log2) - 1;
+  const int n_items = h->n_chunks_norm << sub_log2;        // host checked: fits in int32
   const rk_tensor_desc* descs = reinterpret_cast<const rk_tensor_desc*>(plan + h->off_descs);
   const int32_t* prefix = rk_stage_prefix(
-      reinterpret_cast<const int32_t*>(plan + h->off_prefix_step), n_tensors + 1, s_prefix);
+      reinterpret_cast<const int32_t*>(plan + h->off_prefix_norm), n_tensors + 1, s_prefix);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const size_t stage_bytes = (size_t)tile * 16;
+  const uint32_t stage_bytes = (uint32_t)tile * 16u;
 
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -122,15 +137,16 @@ rk_step_bulk_kernel(const char* __restrict__ plan, const __grid_constant__ Table
   if (warp == 0) {
     // ================= producer (one lane) =================
     if (lane != 0) return;
-    long long it = 0;          // items enqueued so far
-    long long retired = 0;     // items whose stores have been issued
-    // retire item j: wait for the consumers, then write the stage back
-    auto retire = [&](long long j) {
-      const int s = (int)(j % stages);
-      mbar_wait(&s_done[s], (uint32_t)((j / stages) & 1));
-      const BulkItem& b = s_item[s];
-      if (b.mode == 0 && b.nbulk > 0) {
-        float* sp = reinterpret_cast<float*>(s_ring + (size_t)s * stage_bytes);
+    int it = 0;                 // items enqueued so far ...
+    int it_s = 0;               // ... the ring slot the next one takes
+    int retired = 0;            // items whose stores have been issued ...
+    int rt_s = 0, rt_ph = 0;    // ... slot and mbarrier phase of the next one to retire
+    // retire the oldest unretired item: wait for the consumers, then write the stage back
+    auto retire = [&]() {
+      mbar_wait(&s_done[rt_s], (uint32_t)rt_ph);
+      const BulkItem& b = s_item[rt_s];
+      if (b.nbulk > 0) {
+        float* sp = reinterpret_cast<float*>(s_ring + rt_s * stage_bytes);
         const uint32_t bytes = (uint32_t)b.nbulk * 4u;
         bulk_store(b.P, sp, bytes);
         if (zero_grads) bulk_store(b.G, sp + tile, bytes);
@@ -138,45 +154,55 @@ rk_step_bulk_kernel(const char* __restrict__ plan, const __grid_constant__ Table
         if (Op::kHasV) bulk_store(b.V, sp + 3 * tile, bytes);
       }
       bulk_commit();           // one group per item, empty or not: keeps the accounting uniform
+      ++retired;
+      if (++rt_s == stages) { rt_s = 0; rt_ph ^= 1; }
     };
     auto enqueue = [&](const BulkItem& b) {
       // the slot of item `it` was last used by item it - stages: its stores must have been
       // issued (retire) and must have finished reading shared memory
       if (it >= stages) {
-        while (retired <= it - stages) retire(retired++);
-        // groups committed after item (it - stages): retired - 1 - (it - stages) ... all of
-        // which are younger; allow those to be pending
-        const long long younger = retired - 1 - (it - stages);
+        while (retired <= it - stages) retire();
+        // groups committed after the one of item (it - stages) may stay pending
+        const int younger = retired - 1 - (it - stages);
         if (younger <= 0) bulk_wait_read<0>();
         else if (younger == 1) bulk_wait_read<1>();
         else if (younger == 2) bulk_wait_read<2>();
         else bulk_wait_read<3>();     // conservative for deeper lags
       }
-      const int s = (int)(it % stages);
-      s_item[s] = b;
-      if (b.mode == 0 && b.nbulk > 0) {
-        float* sp = reinterpret_cast<float*>(s_ring + (size_t)s * stage_bytes);
+      s_item[it_s] = b;
+      if (b.nbulk > 0) {
+        float* sp = reinterpret_cast<float*>(s_ring + it_s * stage_bytes);
         const uint32_t bytes = (uint32_t)b.nbulk * 4u;
         const int n_streams = 2 + (b.M != nullptr) + (Op::kHasV ? 1 : 0);
-        mbar_arrive_expect_tx(&s_full[s], bytes * n_streams);
-        bulk_load(sp, b.P, bytes, &s_full[s]);
-        bulk_load(sp + tile, b.G, bytes, &s_full[s]);
-        if (b.M) bulk_load(sp + 2 * tile, b.M, bytes, &s_full[s]);
-        if (Op::kHasV) bulk_load(sp + 3 * tile, b.V, bytes, &s_full[s]);
+        mbar_arrive_expect_tx(&s_full[it_s], bytes * n_streams);
+        bulk_load(sp, b.P, bytes, &s_full[it_s]);
+        bulk_load(sp + tile, b.G, bytes, &s_full[it_s]);
+        if (b.M) bulk_load(sp + 2 * tile, b.M, bytes, &s_full[it_s]);
+        if (Op::kHasV) bulk_load(sp + 3 * tile, b.V, bytes, &s_full[it_s]);
       } else {
-        mbar_arrive(&s_full[s]);
+        mbar_arrive(&s_full[it_s]);
       }
       ++it;
+      if (++it_s == stages) it_s = 0;
     };
     const int lag = stages > 2 ? stages - 2 : 1;   // stages kept loading ahead of the stores
-    for (long long w = blockIdx.x; w < n_items; w += gridDim.x) {
-      const int c = (int)(w / tiles_per_chunk);
-      const int sub = (int)(w - (long long)c * tiles_per_chunk);
-      const int t = rk_find_tensor(prefix, n_tensors, c);
-      const rk_tensor_desc d = descs[t];
-      const int gflags = dtable ? dtable->g[d.group].flags : table.g[d.group].flags;
-      if ((d.flags & RK_TENSOR_SKIP) || (gflags & GROUP_SKIP)) continue;
-      const int64_t base = (int64_t)(c - prefix[t]) * chunk + (int64_t)sub * tile;
+    // the tensor of the previous item is usually the tensor of this one: keep its descriptor
+    int t_lo = 0, t_hi = 0;            // chunk range [t_lo, t_hi) of the cached tensor
+    rk_tensor_desc d;
+    bool d_skip = true;
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+      const int c = w >> sub_log2;
+      const int sub = w & sub_mask;
+      if (c < t_lo || c >= t_hi) {
+        const int t = rk_find_tensor(prefix, n_tensors, c);
+        t_lo = prefix[t];
+        t_hi = prefix[t + 1];
+        d = descs[t];
+        const int gflags = dtable ? dtable->g[d.group].flags : table.g[d.group].flags;
+        d_skip = (d.flags & RK_TENSOR_SKIP) || (gflags & GROUP_SKIP);
+      }
+      if (d_skip) continue;
+      const int64_t base = (int64_t)(c - t_lo) * chunk + ((int64_t)sub << tile_log2);
       const int64_t rem = d.numel - base;
       if (rem <= 0) continue;
       BulkItem b;
@@ -189,7 +215,7 @@ rk_step_bulk_kernel(const char* __restrict__ plan, const __grid_constant__ Table
       b.mode = 0;
       b.nbulk = (d.flags & RK_TENSOR_VEC4) ? (b.count & ~3) : 0;
       // write back finished tiles early enough that `lag` loads stay in flight
-      while (retired < it - lag) retire(retired++);
+      while (retired < it - lag) retire();
       enqueue(b);
     }
     BulkItem e;
@@ -197,32 +223,35 @@ rk_step_bulk_kernel(const char* __restrict__ plan, const __grid_constant__ Table
     e.count = e.nbulk = e.group = 0;
     e.mode = 1;
     enqueue(e);
-    while (retired < it - 1) retire(retired++);   // everything before the end marker
+    while (retired < it - 1) retire();   // everything before the end marker
     bulk_wait_all();
     return;
   }
 
   // ================= consumers =================
+  grid_dependency_wait();      // the norm below is the previous kernel's output
   Prolog pr;
   pr.scale = grad_scale;
   pr.has_scale = grad_scale != 1.0f;
   pr.has_clip = total_norm != nullptr;
-  pr.coef = pr.has_clip ? rk_clip_coef(__ldg(total_norm), max_norm) : 1.0f;
+  pr.coef = pr.has_clip ? rk_clip_coef(__ldcg(total_norm), max_norm) : 1.0f;
   const int ctid = tid - 32;
   constexpr int NC = CW * 32;
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (long long it = 0;; ++it) {
-    const int s = (int)(it % stages);
-    mbar_wait(&s_full[s], (uint32_t)((it / stages) & 1));
+  const int tile4 = tile >> 2;
+  int s = 0;
+  uint32_t ph = 0;
+  for (;;) {
+    mbar_wait(&s_full[s], ph);
     const BulkItem b = s_item[s];
     if (b.mode == 1) break;
     Op op;
     op.h = dtable ? dtable->g[b.group] : table.g[b.group];
     const bool has_m = b.M != nullptr;
-    float4* sp = reinterpret_cast<float4*>(s_ring + (size_t)s * stage_bytes);
-    float4* sg = sp + (tile >> 2);
-    float4* sm = sg + (tile >> 2);
-    float4* sv = sm + (tile >> 2);
+    float4* sp = reinterpret_cast<float4*>(s_ring + s * stage_bytes);
+    float4* sg = sp + tile4;
+    float4* sm = sg + tile4;
+    float4* sv = sm + tile4;
     const int nvec = b.nbulk >> 2;
     for (int i = ctid; i < nvec; i += NC) {
       float4 p4 = sp[i], g4 = sg[i], m4 = zero4, v4 = zero4;
@@ -249,5 +278,6 @@ rk_step_bulk_kernel(const char* __restrict__ plan, const __grid_constant__ Table
     fence_async_smem();        // my shared-memory writes -> visible to the bulk stores
     __syncwarp();
     if (lane == 0) mbar_arrive(&s_done[s]);
+    if (++s == stages) { s = 0; ph ^= 1; }
   }
 }

@@ -22,8 +22,9 @@ pytestmark = pytest.mark.gpu
 
 # (variant number in csrc/rk_step.cu, what it is)
 VARIANTS = [(4, "v4 U2 3cta"), (9, "v4 U1 5cta"), (30, "v8 U1 3cta"), (31, "v8 U1 4cta"),
-            (33, "v8 U1 5cta"), (20, "bulk 16w t2048"), (21, "bulk 16w t4096"),
-            (22, "bulk 8w t2048"), (23, "bulk 16w t1024"), (24, "bulk 8w t1024")]
+            (33, "v8 U1 5cta"), (21, "bulk 16w t4096 pdl"), (20, "bulk 16w t2048"),
+            (22, "bulk 16w t1024"), (23, "bulk 12w t4096"), (24, "bulk 8w t4096"),
+            (25, "bulk 16w t4096 no-pdl")]
 IDS = [f"v{v}-{name.replace(' ', '_')}" for v, name in VARIANTS]
 
 
@@ -113,7 +114,7 @@ def test_sgd_variants_bit_exact(variant, case):
                     assert np.array_equal(_bits(s.m.cpu().numpy()), _bits(h[2])), (variant, i)
 
 
-@pytest.mark.parametrize("variant", [20, 23, 30], ids=["bulk2048", "bulk1024", "v8"])
+@pytest.mark.parametrize("variant", [21, 22, 30], ids=["bulk4096", "bulk1024", "v8"])
 def test_variants_many_tensors_skips_and_guard_words(variant):
     """5000 seven-element tensors (prefix table searched in global memory), every third one
     skipped, one group skipped, all carved out of one allocation per stream with guard words

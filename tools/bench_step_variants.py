@@ -102,13 +102,30 @@ def main() -> None:
                 if i >= 3:
                     tn.append(e[0].elapsed_time(e[1]))
                     ts.append(e[1].elapsed_time(e[2]))
+            # the pair with no event between the two launches (an event record in between
+            # would turn a programmatic dependent launch back into a full dependency)
+            tp = []
+            for i in range(args.iters + 3):
+                flat["g"].normal_(0, 1e-3)
+                if small:
+                    flush.fill_(float(i))
+                e = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+                e[0].record()
+                norm = be.l2norm(plan, 1.0)
+                be.adam_step(plan, [dict(hp, step=i + 1)], norm, 1.0, 1.0, True)
+                e[1].record()
+                torch.cuda.synchronize()
+                if i >= 3:
+                    tp.append(e[0].elapsed_time(e[1]))
             t_step, t_norm = statistics.mean(ts), statistics.mean(tn)
             row = {"layout": name, "params": n, "tensors": len(sizes), "variant": v,
                    "step_ms": round(t_step, 5), "step_ms_min": round(min(ts), 5),
                    "norm_ms": round(t_norm, 5),
                    "step_gbs": round(32 * n / t_step / 1e6, 1),
                    "step_gbs_best": round(32 * n / min(ts) / 1e6, 1),
-                   "full_gbs_36B": round(36 * n / (t_step + t_norm) / 1e6, 1)}
+                   "full_gbs_36B": round(36 * n / (t_step + t_norm) / 1e6, 1),
+                   "pair_ms": round(statistics.mean(tp), 5),
+                   "pair_gbs_36B": round(36 * n / statistics.mean(tp) / 1e6, 1)}
             rows.append(row)
             print(json.dumps(row), flush=True)
         lib.rk_step_variant_override(-1)
