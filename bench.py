@@ -4,20 +4,32 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload (BASELINE.json configs[1]): ResNet-18 (num_classes=10) on synthetic CIFAR-10-shaped
-3x32x32 batches, bs=256 per GPU, AdamW(lr=1e-3, wd=1e-2) + global-norm clip 1.0, fp32,
-driven through the unchanged capsule API (Launcher > Looper > Dataset/Module/Loss/
-Optimizer).  One "step" is one Looper iteration.
+Headline workload (BASELINE.json configs[1]): ResNet-18 (num_classes=10) on synthetic
+CIFAR-10-shaped 3x32x32 batches, bs=256 per GPU, AdamW(lr=1e-3, wd=1e-2) + global-norm clip
+1.0, true fp32 (TF32 off, as in the parity tests), driven through the unchanged capsule API
+(Launcher > Looper > Dataset/Module/Loss/Optimizer).  One "step" is one Looper iteration.
 
 Prints ONE JSON line (rank 0):
-  value     train samples/s, whole job, batch already resident in HBM when timing starts
-  e2e       same metric through the public API with HOST batches: pinned-ring H2D staging and
-            the loss read back to the host are inside the timed region
-  roofline  the fused AdamW step kernel: algorithmic 32 B/param / CUDA-event duration measured
-            live in the timed region, against MEASURED_PEAKS.json
-  optstep   config[4] microbench (fused norm+AdamW+zero over 1e9 fp32 params), same kernels
+  value         train samples/s, whole job, batch already resident in HBM when timing starts
+  e2e           same metric through the public API with HOST batches: pinned-ring H2D staging
+                and the loss read back to the host are inside the timed region
+  roofline      the fused AdamW step kernel: algorithmic 32 B/param / CUDA-event duration
+                measured live in the timed region, against MEASURED_PEAKS.json
+  eager         the same workload without the additive Module(graph=True) keyword: what an
+                unchanged reference script gets
+  torch_gpu     baseline B: stock torch on the same GPU(s), no capsules: AdamW(fused=True) +
+                clip_grad_norm_(foreach=True) + zero_grad(set_to_none=True), DDP at N > 1
+  resnet50      configs[2] (ResNet-50, 3x224x224, bs 256/GPU, bf16 autocast), value + e2e
+  gpt2          configs[3] (GPT-2 small, seq 1024, micro-batch 8, accum 4), at 8 GPUs
+  optstep       configs[4] microbench (fused norm+AdamW+zero over 1e9 fp32 params): one flat
+                tensor and the realistic list (GPT-2's 148 shapes x 8 + pad), and stock torch
+                (clip_grad_norm_ foreach + AdamW fused) on the same tensors; at N > 1 the
+                data-parallel step (fused NVLink exchange + step) replicated and sharded
+  parity_check  N > 1 only, before anything is timed: the exchange kernel against an fp64 host
+                sum and the oracle norm, the sharded step against the replicated one bit for
+                bit, and (after the timed run) replicas bit-identical; any mismatch exits 1
   cpu_baseline  the looper port (torch.optim foreach=False) on this box's host cores,
-            bounded sample
+                bounded sample
 
 --impl reference times that CPU port alone, with all host threads (the reference itself is
 pure Python + torch and is not present on the GPU box; oracle/looper_port.py restates it).
@@ -25,6 +37,7 @@ pure Python + torch and is not present on the GPU box; oracle/looper_port.py res
 from __future__ import annotations
 
 import argparse
+import importlib.util
 import json
 import os
 import statistics
@@ -45,16 +58,23 @@ BATCH = 256
 METRIC = "train samples/sec (ResNet-18 CIFAR-shaped bs=256/GPU, AdamW+clip) + fused-step HBM GB/s"
 ALGO_BYTES_STEP = 32      # AdamW update 28 B + grad zero-fill 4 B per fp32 param (K2)
 ALGO_BYTES_NORM = 4       # K1
+STEP_KERNEL = "rk_step_bulk_kernel<AdamOp,AdamTable,16>"   # what the library picks by default
 
 
-def measured_traffic():
-    """DRAM bytes per launch of the step kernel in this workload, from the committed ncu
-    --set full capture (profiles/r1_roofline.json); None if no capture is on record."""
-    p = ROOT / "profiles" / "r1_roofline.json"
-    try:
-        return json.loads(p.read_text())["resnet18_step_kernel"]["dram_bytes_per_launch"]
-    except Exception:
+def measured_traffic(kernel: str, workload: str):
+    """DRAM bytes per launch of `kernel` inside `workload`'s step, from the committed ncu
+    --set full capture of exactly that kernel (profiles/r2_roofline.json); None if there is no
+    capture of it on record (or a tuning override is active: the capture would not apply)."""
+    if os.environ.get("RK_STEP_VARIANT"):
         return None
+    try:
+        rec = json.loads((ROOT / "profiles" / "r2_roofline.json").read_text())
+        for e in rec["captures"]:
+            if e["kernel"] == kernel and e["workload"] == workload:
+                return e["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
 
 
 def peaks():
@@ -105,7 +125,7 @@ class ClockSampler:
                 "samples": len(self.rows)}
 
 
-# ---- workload ----------------------------------------------------------------------------------
+# ---- workloads -----------------------------------------------------------------------------------
 def make_resnet18():
     import torchvision
     import workloads
@@ -120,8 +140,6 @@ def make_resnet50():
     return workloads.BatchModel(torchvision.models.resnet50())
 
 
-# The default is the driver's headline workload (configs[1]).  `resnet50` is configs[2]
-# (ImageNet-shaped, bf16 autocast, SGD momentum) for the 1 -> 8 GPU scaling target.
 def make_gpt2():
     from transformers import GPT2Config, GPT2LMHeadModel
     torch.manual_seed(0)
@@ -146,59 +164,77 @@ class NextTokenLoss(torch.nn.Module):
             logits[:, :-1].reshape(-1, logits.shape[-1]).float(), ids[:, 1:].reshape(-1))
 
 
+# `resnet18` is the driver's headline workload (configs[1]); `resnet50` is configs[2]
+# (ImageNet-shaped, bf16 autocast, SGD momentum), `gpt2` configs[3].
 WORKLOADS = {
     "gpt2": dict(
         net=make_gpt2, shape=(1024,), classes=50257, mixed_precision="bf16", max_norm=1.0,
-        batch=8, accum=4, tokens=True,
+        batch=8, accum=4, tokens=True, algo=ALGO_BYTES_STEP,
         opt=lambda ps: torch.optim.AdamW(ps, lr=6e-4, betas=(0.9, 0.95), weight_decay=0.1),
         label="configs[3]: GPT-2 small 124M (GPT2LMHeadModel), synthetic tokens seq 1024, "
               "micro-batch 8/GPU, grad-accum 4, AdamW(6e-4,(0.9,0.95),wd 0.1)+clip 1.0, bf16 "
               "autocast, capsule API", dtype="bf16 autocast / f32 master"),
     "resnet18": dict(
         net=make_resnet18, shape=(3, 32, 32), classes=10, mixed_precision=None, max_norm=1.0,
+        algo=ALGO_BYTES_STEP,
         opt=lambda ps: torch.optim.AdamW(ps, lr=1e-3, weight_decay=1e-2),
         label="configs[1]: ResNet-18(num_classes=10), synthetic 3x32x32, bs=256/GPU, "
               "AdamW(lr=1e-3,wd=1e-2)+clip 1.0, fp32, capsule API", dtype="f32"),
     "resnet50": dict(
         net=make_resnet50, shape=(3, 224, 224), classes=1000, mixed_precision="bf16",
-        max_norm=None, opt=lambda ps: torch.optim.SGD(ps, lr=0.1, momentum=0.9, weight_decay=1e-4),
+        max_norm=None, algo=24,                                   # SGD+momentum: 20 + 4
+        opt=lambda ps: torch.optim.SGD(ps, lr=0.1, momentum=0.9, weight_decay=1e-4),
         label="configs[2]: ResNet-50, synthetic 3x224x224, bs=256/GPU, bf16 autocast, "
               "SGD(momentum 0.9, wd 1e-4), capsule API", dtype="bf16 autocast / f32 master"),
 }
-WL = WORKLOADS["resnet18"]
 
 
-def synthetic_batch(rank: int, n: int | None = None):
-    n = n or WL.get("batch", BATCH)
+def set_precision(wl) -> None:
+    """The line whose dtype says f32 computes in true fp32: TF32 off for convolutions and
+    matmuls, which is also what every parity test runs (tests/test_engine_gpu.py).  The bf16
+    workloads autocast; whatever stays fp32 there keeps torch's defaults."""
+    fp32 = wl["mixed_precision"] is None
+    torch.backends.cudnn.allow_tf32 = not fp32
+    torch.backends.cuda.matmul.allow_tf32 = not fp32
+    torch.backends.cudnn.benchmark = True
+
+
+def synthetic_batch(wl, rank: int, n: int | None = None):
+    n = n or wl.get("batch", BATCH)
     g = torch.Generator().manual_seed(1234 + rank)
-    if WL.get("tokens"):
-        ids = torch.randint(0, WL["classes"], (n, *WL["shape"]), generator=g)
+    if wl.get("tokens"):
+        ids = torch.randint(0, wl["classes"], (n, *wl["shape"]), generator=g)
         return ids, ids[:, 0].clone()
-    return (torch.randn(n, *WL["shape"], generator=g),
-            torch.randint(0, WL["classes"], (n,), generator=g))
+    return (torch.randn(n, *wl["shape"], generator=g),
+            torch.randint(0, wl["classes"], (n,), generator=g))
 
 
-def run_ours(args) -> dict:
+def env_ranks():
+    return (int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)),
+            int(os.environ.get("LOCAL_RANK", 0)))
+
+
+def run_capsule(wl, *, graph: bool, steps: int, warmup: int, e2e: bool, loader_workers: int = 0):
+    """One Launcher.launch() of the capsule graph on `wl`: `warmup` untimed iterations, then
+    exactly `steps` timed ones between two barrier + device-sync fences (CUDA events, max over
+    ranks).  e2e=False: one batch resident in HBM; e2e=True: host batches through
+    rocket.Dataset + the pinned-ring stager, every step's loss read back to the host."""
     import rocket_b200 as rk
     import workloads
     from rocket_b200 import _native
     from rocket_b200.backend import NativeBackend
     from rocket_b200.engine import Engine
 
-    rank = int(os.environ.get("RANK", 0))
-    world = int(os.environ.get("WORLD_SIZE", 1))
-    local = int(os.environ.get("LOCAL_RANK", 0))
-    if os.environ.get("RK_SWITCH"):
-        sys.setswitchinterval(float(os.environ["RK_SWITCH"]))
-    W, K = args.warmup, args.steps
-    TAIL = 8 if args.graph else 0      # synchronised replays after the timed region (kernel timing)
-    assert W >= 3, "timing rules: at least 3 warm-up steps"
-    if args.graph:
+    rank, world, local = env_ranks()
+    W, K = warmup, steps
+    accum = wl.get("accum", 1)
+    TAIL = 8 if graph else 0        # synchronised replays after the timed region (kernel timing)
+    if graph:
         # Module(graph=True) runs GRAPH_WARMUP eager iterations per input signature and then
         # captures: with a short --warmup the capture would land inside the timed region.
         # Extra untimed steps keep it out; the line reports the warm-up actually done.
-        W = max(W, (rk.Module.GRAPH_WARMUP + 2) * WL.get("accum", 1))
-    torch.backends.cudnn.benchmark = True
+        W = max(W, (rk.Module.GRAPH_WARMUP + 2) * accum)
+    set_precision(wl)
 
     class TimedBackend(NativeBackend):
         """Brackets each engine kernel launch with CUDA events on its own stream.  While a
@@ -219,7 +255,7 @@ def run_ours(args) -> dict:
                     if e.query():
                         dt = s.elapsed_time(e)
                         if 0.0 < dt < 20.0:          # a torn pair (replay in flight) is negative
-                            self.graph_ms[key].append(dt)
+                            self.graph_ms.setdefault(key, []).append(dt)
                 except Exception:
                     pass
 
@@ -268,6 +304,8 @@ def run_ours(args) -> dict:
         return eng
 
     rk.Launcher.engine_factory = staticmethod(factory)
+    from rocket_b200.comm import P2PGradSync
+    P2PGradSync.graph_timing = True      # event pair around the exchange inside captured steps
 
     class ResidentBatch(rk.Capsule):
         """Hands the Looper one batch that already lives in HBM (the `value` leg)."""
@@ -293,6 +331,8 @@ def run_ours(args) -> dict:
             self.t1 = torch.cuda.Event(enable_timing=True)
             self.ms = self.launches = None
             self.losses = []
+            self.exchange = None
+            self.sync = None
             self.sampler = ClockSampler(local)
 
         def _fence(self):
@@ -314,6 +354,7 @@ def run_ours(args) -> dict:
                 for sync in self._accelerator._grad_sync.values():
                     if hasattr(sync, "profile"):
                         sync.profile, self.sync = True, sync
+                        sync.graph_ms = []
                 if rank == 0:
                     self.sampler.start()
                 self.t0.record()
@@ -323,6 +364,8 @@ def run_ours(args) -> dict:
                 # in-graph event pairs of the engine kernels can be read
                 torch.cuda.synchronize()
                 be.sample_graph_events()
+                if self.sync is not None:
+                    self.sync.sample_graph_events()
             elif self.i == W + K:
                 if self.read_loss:            # the host must hold every step's loss
                     self.host_losses = [float(v) for v in self.losses]
@@ -330,7 +373,8 @@ def run_ours(args) -> dict:
                 self._fence()
                 be.sample_graph_events()
                 be.timing = False
-                if getattr(self, "sync", None) is not None:
+                if self.sync is not None:
+                    self.sync.sample_graph_events()
                     self.sync.profile = False
                     self.exchange = [(nb, a.elapsed_time(b)) for nb, a, b in self.sync.timings]
                 self.launches = _native.launch_count() \
@@ -338,44 +382,16 @@ def run_ours(args) -> dict:
                 self.clocks = self.sampler.stop() if rank == 0 else None
                 self.ms = self.t0.elapsed_time(self.t1)
 
-    def graph(data_capsule, probe):
-        net = WL["net"]()
-        opt = WL["opt"](net.parameters())
-        objective = NextTokenLoss() if WL.get("tokens") else workloads.CrossEntropy()
-        inner = [rk.Loss(objective=objective),
-                 rk.Optimizer(opt, max_grad_norm=WL["max_norm"])]
-        looper = rk.Looper([data_capsule, rk.Module(net, capsules=inner, graph=args.graph), probe],
-                           tag="bench", repeats=W + K + TAIL)
-        return rk.Launcher([looper], num_epochs=1, mixed_precision=WL["mixed_precision"],
-                           gradient_accumulation_steps=WL.get("accum", 1),
-                           destroy_process_group_after_launch=False), opt
-
-    # ---- leg 1: inputs resident in HBM -----------------------------------------------------------
-    probe = Probe(read_loss=False)
-    launcher, opt = graph(ResidentBatch(synthetic_batch(rank)), probe)
-    launcher.launch()
-    be = holder["engine"].backend
-    n_params = sum(p.numel() for p in opt.param_groups[0]["params"])
-    step_ms = [s.elapsed_time(e) for s, e in be.ev["step"]] + be.graph_ms["step"]
-    norm_ms = [s.elapsed_time(e) for s, e in be.ev["norm"]] + be.graph_ms["norm"]
-    ms = torch.tensor([probe.ms], device="cuda")
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms.item())
-    value = world * WL.get("batch", BATCH) * K / (ms_total / 1e3)
-    launches, clocks = probe.launches, probe.clocks
-
-    # ---- leg 2: end to end, host batches through Dataset + stager ----------------------------------
     class PoolDataset(torch.utils.data.Dataset):
         """(W+K)*world batches of host samples drawn from a fixed synthetic pool."""
         def __init__(self, pool: int, length: int):
             g = torch.Generator().manual_seed(99)
-            if WL.get("tokens"):
-                self.x = torch.randint(0, WL["classes"], (pool, *WL["shape"]), generator=g)
+            if wl.get("tokens"):
+                self.x = torch.randint(0, wl["classes"], (pool, *wl["shape"]), generator=g)
                 self.y = self.x[:, 0].clone()
             else:
-                self.x = torch.randn(pool, *WL["shape"], generator=g)
-                self.y = torch.randint(0, WL["classes"], (pool,), generator=g)
+                self.x = torch.randn(pool, *wl["shape"], generator=g)
+                self.y = torch.randint(0, wl["classes"], (pool,), generator=g)
             self.length = length
 
         def __len__(self):
@@ -385,120 +401,409 @@ def run_ours(args) -> dict:
             j = i % self.x.shape[0]
             return self.x[j], self.y[j]
 
-    B = WL.get("batch", BATCH)
-    pool = 16 * B if WL["shape"][-1] <= 64 or WL.get("tokens") else 2 * B
-    host_ds = PoolDataset(pool=pool, length=(W + K + TAIL) * B * world)
-    probe2 = Probe(read_loss=True)
-    # an ordinary input pipeline: DataLoader kwargs pass straight through rocket.Dataset
-    launcher2, _ = graph(rk.Dataset(host_ds, batch_size=B, shuffle=False,
-                                    num_workers=args.loader_workers,
-                                    prefetch_factor=4 if args.loader_workers else None),
-                         probe2)
-    launcher2.launch()
-    ms2 = torch.tensor([probe2.ms], device="cuda")
-    if world > 1:
-        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-    e2e_value = world * B * K / (float(ms2.item()) / 1e3)
-    sample_bytes = 8 * WL["shape"][0] if WL.get("tokens") else \
-        4 * WL["shape"][0] * WL["shape"][1] * WL["shape"][2]
-    h2d = B * (sample_bytes + 8)
+    B = wl.get("batch", BATCH)
+    probe = Probe(read_loss=e2e)
+    if e2e:
+        pool = 16 * B if wl["shape"][-1] <= 64 or wl.get("tokens") else 2 * B
+        host_ds = PoolDataset(pool=pool, length=(W + K + TAIL) * B * world)
+        # an ordinary input pipeline: DataLoader kwargs pass straight through rocket.Dataset
+        data = rk.Dataset(host_ds, batch_size=B, shuffle=False, num_workers=loader_workers,
+                          prefetch_factor=4 if loader_workers else None)
+    else:
+        data = ResidentBatch(synthetic_batch(wl, rank))
+    net = wl["net"]()
+    opt = wl["opt"](net.parameters())
+    objective = NextTokenLoss() if wl.get("tokens") else workloads.CrossEntropy()
+    inner = [rk.Loss(objective=objective), rk.Optimizer(opt, max_grad_norm=wl["max_norm"])]
+    looper = rk.Looper([data, rk.Module(net, capsules=inner, graph=bool(graph)), probe],
+                       tag="bench", repeats=W + K + TAIL)
+    launcher = rk.Launcher([looper], num_epochs=1, mixed_precision=wl["mixed_precision"],
+                           gradient_accumulation_steps=accum,
+                           destroy_process_group_after_launch=False)
+    launcher.launch()
 
+    be = holder["engine"].backend
+    params = list(opt.param_groups[0]["params"])
+    n_params = sum(p.numel() for p in params)
+    step_ms = [s.elapsed_time(e) for s, e in be.ev["step"]] + be.graph_ms.get("step", [])
+    norm_ms = [s.elapsed_time(e) for s, e in be.ev["norm"]] + be.graph_ms.get("norm", [])
+    ms = torch.tensor([probe.ms], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    res = {"ms_total": ms_total, "ms_per_step": ms_total / K, "steps": K, "warmup": W,
+           "value": world * B * K / (ms_total / 1e3), "launches": probe.launches,
+           "clocks": probe.clocks, "step_ms": step_ms, "norm_ms": norm_ms,
+           "n_params": n_params, "batch": B, "accum": accum,
+           "grad_sync": (holder["engine"].grad_sync_kinds or ["none"])[0],
+           "exchange": probe.exchange,
+           "exchange_graph_ms": list(getattr(probe.sync, "graph_ms", []) or []),
+           "exchange_graph_bytes": getattr(probe.sync, "graph_bytes", 0)}
+    if world > 1:
+        import parity_checks
+        res["replicas_identical"] = parity_checks.replicas_identical(
+            params + [b for b in net.buffers() if b.dtype.is_floating_point],
+            torch.device("cuda", local))
+    if e2e:
+        sample_bytes = 8 * wl["shape"][0] if wl.get("tokens") else \
+            4 * wl["shape"][0] * wl["shape"][1] * wl["shape"][2]
+        res["h2d_bytes_per_step"] = B * (sample_bytes + 8)
+        res["losses_read"] = len(getattr(probe, "host_losses", []))
+    del launcher, looper, net, opt, holder
+    torch.cuda.empty_cache()
+    return res
+
+
+def exchange_summary(res, world: int):
+    """K6 as timed inside the run: eager mode brackets every bucket's kernel with events on
+    the side stream; graph mode records external event pairs inside the captured step."""
+    K = res["steps"]
+    if res.get("exchange"):
+        nbytes = sum(nb for nb, _ in res["exchange"])
+        ms_x = sum(t for _, t in res["exchange"])
+        per_step_ms, per_step_bytes = ms_x / K, nbytes // K
+        launches = round(len(res["exchange"]) / K, 2)
+        how = "CUDA events around every bucket's kernel on the exchange stream (eager step)"
+    elif res.get("exchange_graph_ms"):
+        per_step_ms = statistics.mean(res["exchange_graph_ms"])
+        per_step_bytes = res["exchange_graph_bytes"]
+        launches = None
+        how = ("external CUDA events inside the replayed graph, first bucket launch to last "
+               "bucket end; read for the last replay of the timed region and 8 synchronised "
+               "replays after it")
+    else:
+        return None
+    bus = 2 * (world - 1) / world * per_step_bytes / (per_step_ms * 1e-3) / 1e9
+    return {"kernel": "rk_allreduce_norm_kernel (NVLink all-reduce + 1/W + norm partials)",
+            "launches_per_step": launches, "bytes_per_step": per_step_bytes,
+            "kernel_ms_per_step": round(per_step_ms, 4), "bus_gbs": round(bus, 1),
+            "nvlink_peak_gbs": 770.0, "frac": round(bus / 770.0, 4), "timing": how,
+            "note": "bus GB/s = 2(W-1)/W x bytes / time = bytes crossing NVLink per direction "
+                    "per GPU; peak = measured peer-copy bandwidth (B200_PROFILING.md); the "
+                    "span includes waiting for the slowest rank's backward"}
+
+
+def capsule_object(wl, res, res_e2e, peak):
+    """A secondary workload's numbers, in the same terms as the headline line."""
+    k2 = statistics.mean(res["step_ms"]) if res["step_ms"] else None
+    out = {"workload": wl["label"], "dtype": wl["dtype"], "value": round(res["value"], 1),
+           "unit": "samples/s", "ms_per_step": round(res["ms_per_step"], 4),
+           "steps": res["steps"], "warmup": res["warmup"], "params": res["n_params"],
+           "global_batch": res["batch"] * res["accum"] * env_ranks()[1],
+           "grad_sync": res["grad_sync"]}
+    if k2:
+        gbs = wl["algo"] * res["n_params"] / (k2 * 1e-3) / 1e9
+        out["step_kernel_ms"] = round(k2, 5)
+        out["step_kernel_gbs"] = round(gbs, 1)
+        out["step_kernel_frac_of_measured_peak"] = round(gbs / peak, 4)
+        out["algorithmic_bytes_per_param"] = wl["algo"]
+    if res["norm_ms"]:
+        out["norm_kernel_ms"] = round(statistics.mean(res["norm_ms"]), 5)
+    if res_e2e is not None:
+        out["e2e"] = {"value": round(res_e2e["value"], 1), "unit": "samples/s",
+                      "ms_per_step": round(res_e2e["ms_per_step"], 4),
+                      "h2d_bytes_per_step": res_e2e["h2d_bytes_per_step"],
+                      "d2h_bytes_per_step": 8}
+    x = exchange_summary(res, env_ranks()[1])
+    if x:
+        out["exchange"] = x
+    if "replicas_identical" in res:
+        out["replicas_bit_identical"] = res["replicas_identical"]
+    return out
+
+
+def torch_gpu_baseline(wl, steps: int, warmup: int):
+    """Baseline B: the same step with stock torch on the same GPU(s)
+    and no capsules -- torch.optim.AdamW(fused=True) + clip_grad_norm_(foreach=True) +
+    zero_grad(set_to_none=True), DistributedDataParallel at N > 1.  That is the strongest path
+    the reference's Optimizer capsule reaches on a GPU today (rocket/core/optimizer.py:129-130
+    with a fused torch optimizer).  Batch resident in HBM, eager, same precision settings."""
+    import workloads
+    rank, world, local = env_ranks()
+    dev = torch.device("cuda", local)
+    set_precision(wl)
+    net = wl["net"]().to(dev)
+    model = net
+    if world > 1:
+        model = torch.nn.parallel.DistributedDataParallel(net, device_ids=[local])
+    if wl["max_norm"] is not None or "AdamW" in wl["label"]:
+        opt = torch.optim.AdamW(net.parameters(), lr=1e-3, weight_decay=1e-2, fused=True)
+    else:
+        opt = torch.optim.SGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4,
+                              fused=True)
+    obj = workloads.CrossEntropy()
+    batch = [t.to(dev) for t in synthetic_batch(wl, rank)]
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ac = torch.autocast("cuda", dtype=torch.bfloat16) if wl["mixed_precision"] == "bf16" \
+        else torch.autocast("cuda", enabled=False)
+    model.train()
+    for i in range(warmup + steps):
+        if i == warmup:
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+                torch.cuda.synchronize()
+            t0.record()
+        with ac:
+            loss = obj(model(batch))
+        loss.backward()
+        if wl["max_norm"] is not None:
+            torch.nn.utils.clip_grad_norm_(net.parameters(), wl["max_norm"], foreach=True)
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+    t1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
+    if world > 1:
+        dist.barrier()
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    B = wl.get("batch", BATCH)
+    del model, net, opt, batch
+    torch.cuda.empty_cache()
+    return {"value": round(world * B * steps / (ms_total / 1e3), 1), "unit": "samples/s",
+            "ms_per_step": round(ms_total / steps, 4), "steps": steps, "warmup": warmup,
+            "what": "stock torch, no capsules: torch.optim.AdamW(fused=True) + "
+                    "clip_grad_norm_(foreach=True) + zero_grad(set_to_none=True)"
+                    + (", DistributedDataParallel" if world > 1 else "")
+                    + "; batch resident in HBM, eager launches, same precision flags"}
+
+
+def parity_check(rank: int, world: int, local: int):
+    """N > 1, before anything is timed (the driver's GPU-test box has one GPU, so this is
+    where the 2/4/8-GPU parity evidence is produced).  Any mismatch raises."""
+    import parity_checks
+    from rocket_b200.backend import NativeBackend
+    dev = torch.device("cuda", local)
+    be = NativeBackend(dev)
+    out = {"world": world}
+    out["exchange_p2p"] = parity_checks.exchange_check(be, rank, world, dev, multicast=False)
+    mc = parity_checks.exchange_check(be, rank, world, dev, multicast=True)
+    out["exchange_multimem"] = mc if mc is not None else "no NVSwitch multicast mapping on this box"
+    out["sharded_step_adamw_p2p"] = parity_checks.sharded_step_check(
+        be, rank, world, dev, multicast=False, kind="adamw", compact=True)
+    out["sharded_step_sgd_p2p"] = parity_checks.sharded_step_check(
+        be, rank, world, dev, multicast=False, kind="sgd", compact=True)
+    mcs = parity_checks.sharded_step_check(be, rank, world, dev, multicast=True, kind="adamw",
+                                           compact=True)
+    out["sharded_step_adamw_multimem"] = mcs if mcs is not None else \
+        "no NVSwitch multicast mapping on this box"
+    out["all_true"] = True          # reached only if no check raised
+    return out
+
+
+def run_ours(args) -> dict:
+    rank, world, local = env_ranks()
+    if os.environ.get("RK_SWITCH"):
+        sys.setswitchinterval(float(os.environ["RK_SWITCH"]))
+    assert args.warmup >= 3, "timing rules: at least 3 warm-up steps"
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+    wl = WORKLOADS[args.workload]
     peak, peak_src = peaks()
-    k2_ms = statistics.mean(step_ms) if step_ms else float("nan")
-    algo = 24 if args.workload == "resnet50" else ALGO_BYTES_STEP   # SGD+momentum: 20 + 4
-    achieved = algo * n_params / (k2_ms * 1e-3) / 1e9
+    extras = args.workload == "resnet18" and not args.lean
+
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = parity_check(rank, world, local)
+
+    # ---- headline: inputs resident in HBM, then end to end from host batches ---------------------
+    res = run_capsule(wl, graph=args.graph, steps=args.steps, warmup=args.warmup, e2e=False)
+    res2 = run_capsule(wl, graph=args.graph, steps=args.steps, warmup=args.warmup, e2e=True,
+                       loader_workers=args.loader_workers)
+    K, W = res["steps"], res["warmup"]
+    k2_ms = statistics.mean(res["step_ms"]) if res["step_ms"] else float("nan")
+    algo = wl["algo"]
+    achieved = algo * res["n_params"] / (k2_ms * 1e-3) / 1e9
+    kernel = STEP_KERNEL if algo == ALGO_BYTES_STEP else STEP_KERNEL.replace("Adam", "Sgd")
     out = {
-        "metric": METRIC, "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
-        "steps": K, "warmup": W, "ms_per_step": round(ms_total / K, 4),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": WL["dtype"],
+        "metric": METRIC, "value": round(res["value"], 1), "unit": "samples/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": round(res["ms_per_step"], 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl["dtype"],
         "data": "synthetic",
-        "config": {"workload": WL["label"],
-                   "global_batch": WL.get("batch", BATCH) * world * WL.get("accum", 1),
+        "config": {"workload": wl["label"],
+                   "global_batch": res["batch"] * world * res["accum"],
                    "parallelism": f"dp{world}",
-                   "grad_sync": (holder["engine"].grad_sync_kinds or ["none"])[0],
+                   "grad_sync": res["grad_sync"],
                    "cuda_graph_step": bool(args.graph),
+                   "tf32": wl["mixed_precision"] is not None,     # off for the f32 workload
                    "l2": "no explicit flush: per-step working set (45 MB x4 optimizer streams "
                          "+ activations of bs 256) exceeds the 126 MB L2",
-                   "params": n_params},
-        "e2e": {"value": round(e2e_value, 1), "unit": "samples/s",
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                "ms_per_step": round(float(ms2.item()) / K, 4),
+                   "params": res["n_params"],
+                   "accelerate_installed": importlib.util.find_spec("accelerate") is not None},
+        "e2e": {"value": round(res2["value"], 1), "unit": "samples/s",
+                "h2d_bytes_per_step": res2["h2d_bytes_per_step"], "d2h_bytes_per_step": 8,
+                "ms_per_step": round(res2["ms_per_step"], 4),
                 "loader_workers": args.loader_workers},
-        "gpu_launches": launches,
-        "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "rk_step_kernel<AdamOp> (fused AdamW+clip+zero)",
+        "gpu_launches": res["launches"],
+        "clocks": res["clocks"],
+        "roofline": {"bound": "hbm", "kernel": kernel + " (fused AdamW+clip+zero)",
                      "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4),
-                     "traffic": measured_traffic() if args.workload == "resnet18" else None,
+                     "traffic": measured_traffic(kernel, args.workload),
                      "peak_source": peak_src, "algorithmic_bytes_per_param": algo,
-                     "launch_ms": round(k2_ms, 5), "launches_timed": len(step_ms),
+                     "launch_ms": round(k2_ms, 5), "launches_timed": len(res["step_ms"]),
                      "timing": ("external CUDA events recorded inside the replayed graph; read for "
                                 "the last replay of the timed region and for 8 synchronised "
                                 "replays right after it") if args.graph else
                                "CUDA events around every launch of the timed region",
-                     "norm_kernel_ms": round(statistics.mean(norm_ms), 5) if norm_ms else None,
+                     "norm_kernel_ms": round(statistics.mean(res["norm_ms"]), 5)
+                     if res["norm_ms"] else None,
                      "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
     }
-    if world > 1 and getattr(probe, "exchange", None):
-        # K6, measured live: the fused NVLink all-reduce + 1/W + norm kernels of the timed region
-        nbytes = sum(nb for nb, _ in probe.exchange)
-        ms_x = sum(t for _, t in probe.exchange)
-        bus = 2 * (world - 1) / world * nbytes / (ms_x * 1e-3) / 1e9
-        out["exchange"] = {
-            "kernel": "rk_allreduce_norm_kernel (NVLink P2P all-reduce + 1/W + norm partials)",
-            "launches_per_step": round(len(probe.exchange) / K, 2),
-            "bytes_per_step": nbytes // K, "kernel_ms_per_step": round(ms_x / K, 4),
-            "bus_gbs": round(bus, 1), "nvlink_peak_gbs": 770.0,
-            "frac": round(bus / 770.0, 4),
-            "note": "bus GB/s = 2(W-1)/W x bytes / kernel time = bytes crossing NVLink per "
-                    "direction per GPU; peak = measured peer-copy bandwidth (B200_PROFILING.md); "
-                    "kernel time includes waiting for the slowest rank's backward"}
+    if world > 1:
+        x = exchange_summary(res, world)
+        if x:
+            out["exchange"] = x
+        ok = bool(res.get("replicas_identical")) and bool(res2.get("replicas_identical"))
+        if parity is not None:
+            parity["replicas_bit_identical_after_timed_runs"] = ok
+            parity["all_true"] = parity["all_true"] and ok
+            out["parity_check"] = parity
+        if not ok:
+            if rank == 0:
+                print(json.dumps({"parity_check": "FAILED: replicas differ after the timed run",
+                                  "resident": res.get("replicas_identical"),
+                                  "e2e": res2.get("replicas_identical")}), flush=True)
+            sys.exit(1)
+
+    if extras:
+        # what an unchanged reference script gets: no Module(graph=True)
+        if args.graph:
+            eg = run_capsule(wl, graph=False, steps=min(K, 50), warmup=max(5, args.warmup // 2),
+                             e2e=False)
+            out["eager"] = {"value": round(eg["value"], 1), "unit": "samples/s",
+                            "ms_per_step": round(eg["ms_per_step"], 4), "steps": eg["steps"],
+                            "cuda_graph_step": False,
+                            "note": "same workload without the additive Module(graph=True) "
+                                    "keyword (resident batch)"}
+            xe = exchange_summary(eg, world)
+            if xe:
+                out["eager"]["exchange"] = xe
+        out["torch_gpu"] = torch_gpu_baseline(wl, steps=min(K, 50), warmup=max(5, args.warmup // 2))
+        # configs[2]: the workload the north_star puts the >= 7x scaling target on
+        w50 = WORKLOADS["resnet50"]
+        r50 = run_capsule(w50, graph=False, steps=args.r50_steps, warmup=5, e2e=False)
+        r50e = run_capsule(w50, graph=False, steps=args.r50_steps, warmup=5, e2e=True,
+                           loader_workers=args.loader_workers)
+        out["resnet50"] = capsule_object(w50, r50, r50e, peak)
+        # configs[3]: 8 GPUs (or on request)
+        if world == 8 or os.environ.get("ROCKET_B200_BENCH_GPT2") == "1":
+            wg = WORKLOADS["gpt2"]
+            g2 = run_capsule(wg, graph=False, steps=16, warmup=8, e2e=False)
+            out["gpt2"] = capsule_object(wg, g2, None, peak)
+            out["gpt2"]["tokens_per_s"] = round(g2["value"] * 1024, 1)
+            out["gpt2"]["optimizer_steps_timed"] = 16 // wg["accum"]
     if world > 1 and not args.no_optstep and out["config"]["grad_sync"].startswith("P2PGradSync"):
         out["optstep"] = optstep_microbench_dp(peak, rank, world, local)
-    if rank == 0 and world == 1 and not args.no_optstep:
+    if world == 1 and not args.no_optstep:
         out["optstep"] = optstep_microbench(peak)
     if rank == 0 and world == 1 and not args.no_cpu and args.workload == "resnet18":
-        out["cpu_baseline"] = cpu_port(budget_s=args.cpu_budget, threads=None, as_line=False)
+        out["cpu_baseline"] = cpu_port(budget_s=args.cpu_budget, threads=None)
     return out
 
 
+def gpt2_shapes():
+    s = [50257 * 768, 1024 * 768]
+    for _ in range(12):
+        s += [768, 768, 768 * 2304, 2304, 768 * 768, 768, 768, 768, 768 * 3072, 3072,
+              3072 * 768, 768]
+    return s + [768, 768]
+
+
 def optstep_microbench(peak: float, n: int = 1_000_000_000, steps: int = 20, warmup: int = 5):
-    """configs[4]: fused norm + AdamW + clip + zero_grad over 1e9 fp32 params (one flat
-    tensor, 16 GB of state: far larger than L2), timed per kernel with CUDA events."""
+    """configs[4]: fused norm + AdamW + clip + zero_grad over 1e9 fp32 params (16 GB of state:
+    far larger than L2), timed per kernel with CUDA events, on the two tensor lists SURVEY
+    8(d) names: (i) one flat tensor, (ii) GPT-2-small's 148 shapes x 8 plus a pad tensor.  Then
+    stock torch on the flat tensor: clip_grad_norm_(foreach=True) + AdamW(fused=True)."""
     from rocket_b200.backend import NativeBackend, TensorSpec
     dev = torch.device("cuda", torch.cuda.current_device())
     be = NativeBackend(dev)
-    p = torch.randn(n, device=dev) * 0.02
-    g = torch.empty(n, device=dev)
-    m = torch.zeros(n, device=dev)
-    v = torch.zeros(n, device=dev)
-    plan = be.make_plan([TensorSpec(p=p, g=g, m=m, v=v, group=0)])
     hp = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2, decoupled=True)
-    tn, ts = [], []
-    for i in range(warmup + steps):
-        g.normal_(0, 1e-3)                                  # fresh grads: clipping is active
-        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+
+    def ours(sizes):
+        offs, off = [], 0
+        for k in sizes:
+            offs.append(off)
+            off += (k + 63) // 64 * 64                       # 256-byte aligned, like flat.py
+        flat = {k: torch.zeros(off, device=dev) for k in "pgmv"}
+        flat["p"].normal_(0, 0.02)
+        plan = be.make_plan([TensorSpec(*[flat[k][o:o + m] for k in "pgmv"], group=0)
+                             for o, m in zip(offs, sizes)])
+        tn, ts, tp = [], [], []
+        for i in range(warmup + steps):
+            flat["g"].normal_(0, 1e-3)                          # fresh grads: clipping is active
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            e[0].record()
+            norm = be.l2norm(plan, 1.0)
+            e[1].record()
+            be.adam_step(plan, [dict(hp, step=i + 1)], norm, 1.0, 1.0, True)
+            e[2].record()
+            torch.cuda.synchronize()
+            if i >= warmup:
+                tn.append(e[0].elapsed_time(e[1]))
+                ts.append(e[1].elapsed_time(e[2]))
+        for i in range(3 + steps // 2):      # the pair back to back (no event between them:
+            flat["g"].normal_(0, 1e-3)       # the step kernel starts as a programmatic dependent)
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            e[0].record()
+            norm = be.l2norm(plan, 1.0)
+            be.adam_step(plan, [dict(hp, step=warmup + steps + i + 1)], norm, 1.0, 1.0, True)
+            e[1].record()
+            torch.cuda.synchronize()
+            if i >= 3:
+                tp.append(e[0].elapsed_time(e[1]))
+        del flat, plan
+        torch.cuda.empty_cache()
+        t_norm, t_step, t_pair = statistics.mean(tn), statistics.mean(ts), statistics.mean(tp)
+        total = sum(sizes)
+        gbs_step = ALGO_BYTES_STEP * total / (t_step * 1e-3) / 1e9
+        gbs_full = (ALGO_BYTES_STEP + ALGO_BYTES_NORM) * total / (t_pair * 1e-3) / 1e9
+        return {"tensors": len(sizes), "step_kernel_ms": round(t_step, 4),
+                "norm_kernel_ms": round(t_norm, 4), "pair_ms": round(t_pair, 4),
+                "step_kernel_gbs": round(gbs_step, 1),
+                "norm_kernel_gbs": round(ALGO_BYTES_NORM * total / (t_norm * 1e-3) / 1e9, 1),
+                "full_step_gbs_36B": round(gbs_full, 1),
+                "step_kernel_frac_of_measured_peak": round(gbs_step / peak, 4),
+                "frac_of_measured_peak": round(gbs_full / peak, 4),
+                "frac_of_nominal_8000": round(gbs_full / 8000.0, 4)}
+
+    flat_res = ours([n])
+    lst = gpt2_shapes() * 8
+    lst = lst + [n - sum(lst)]
+    list_res = ours(lst)
+
+    # stock torch on the flat tensor: what the reference's Optimizer capsule reaches today with
+    # a fused torch optimizer, plus the clipping pass (28 + 12 B/param of traffic)
+    p = torch.nn.Parameter(torch.randn(n, device=dev) * 0.02)
+    p.grad = torch.empty(n, device=dev)
+    topt = torch.optim.AdamW([p], lr=1e-3, weight_decay=1e-2, fused=True)
+    tt = []
+    for i in range(3 + steps // 2):
+        p.grad.normal_(0, 1e-3)
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         e[0].record()
-        norm = be.l2norm(plan, 1.0)
+        torch.nn.utils.clip_grad_norm_([p], 1.0, foreach=True)
+        topt.step()
+        p.grad.zero_()                      # persistent gradients, like ours (4 B/param more)
         e[1].record()
-        be.adam_step(plan, [dict(hp, step=i + 1)], norm, 1.0, 1.0, True)
-        e[2].record()
         torch.cuda.synchronize()
-        if i >= warmup:
-            tn.append(e[0].elapsed_time(e[1]))
-            ts.append(e[1].elapsed_time(e[2]))
-    del p, g, m, v
+        if i >= 3:
+            tt.append(e[0].elapsed_time(e[1]))
+    del p, topt
     torch.cuda.empty_cache()
-    t_norm, t_step = statistics.mean(tn), statistics.mean(ts)
-    gbs_step = ALGO_BYTES_STEP * n / (t_step * 1e-3) / 1e9
-    gbs_norm = ALGO_BYTES_NORM * n / (t_norm * 1e-3) / 1e9
-    gbs_full = (ALGO_BYTES_STEP + ALGO_BYTES_NORM) * n / ((t_step + t_norm) * 1e-3) / 1e9
-    return {"params": n, "layout": "one flat fp32 tensor", "steps": steps,
-            "step_kernel_ms": round(t_step, 4), "norm_kernel_ms": round(t_norm, 4),
-            "step_kernel_gbs": round(gbs_step, 1), "norm_kernel_gbs": round(gbs_norm, 1),
-            "full_step_gbs_36B": round(gbs_full, 1),
-            "frac_of_measured_peak": round(gbs_full / peak, 4),
-            "frac_of_nominal_8000": round(gbs_full / 8000.0, 4)}
+    t_torch = statistics.mean(tt)
+    out = {"params": n, "layout": "one flat fp32 tensor", "steps": steps}
+    out.update(flat_res)
+    out["realistic_list"] = dict(list_res, layout="GPT-2-small's 148 shapes x 8 + one pad "
+                                                  "tensor, 256-byte aligned segments")
+    out["torch_fused_ms"] = round(t_torch, 4)
+    out["torch_fused_what"] = ("clip_grad_norm_(foreach=True) + torch.optim.AdamW(fused=True)"
+                               ".step() + grad.zero_() on the same flat tensor")
+    out["speedup_vs_torch_fused"] = round(t_torch / flat_res["pair_ms"], 3)
+    return out
 
 
 def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
@@ -514,10 +819,9 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
     be = NativeBackend(dev)
     sig = N.RK_COMM_SIGNAL_BYTES
     scratch = -(-be.scratch_bytes([n]) // 256) * 256
-    # Sharded arm: hardware-validated this round at 2 and 4 GPUs (gpurun budget); at 8 it (and
-    # the parameter half of the arena it needs) is there only on request, so that the default
-    # bench line never depends on an unvalidated configuration.
-    run_sharded = world in (2, 4) or os.environ.get("ROCKET_B200_BENCH_SHARDED") == "1"
+    # Sharded arm at every world size (validated bit for bit against the replicated step by
+    # parity_check above, on this very run, before anything is timed).
+    run_sharded = os.environ.get("ROCKET_B200_BENCH_SHARDED", "1") == "1"
     arena = alloc_arena(sig + scratch + (8 if run_sharded else 4) * n, dev)  # [signals|scratch|g|p]
     g = arena[sig + scratch:sig + scratch + 4 * n].view(torch.float32)
     p = arena[sig + scratch + 4 * n:].view(torch.float32) if run_sharded \
@@ -607,15 +911,16 @@ def optstep_microbench_dp(peak: float, rank: int, world: int, local: int,
                 round(ALGO_BYTES_STEP * n / (t_s * 1e-3) / 1e9 / peak, 4)}
 
 
-def cpu_port(budget_s: float, threads, as_line: bool, steps=None, warmup=1):
+def cpu_port(budget_s: float, threads, steps=None, warmup=1):
     """The looper port on the host cores: ResNet-18 bs=256, AdamW(foreach=False) + clip."""
     import workloads
     from oracle import looper_port
     if threads:
         torch.set_num_threads(threads)
+    wl = WORKLOADS["resnet18"]
     net = make_resnet18()
     opt = torch.optim.AdamW(net.parameters(), lr=1e-3, weight_decay=1e-2, foreach=False)
-    batch = synthetic_batch(0)
+    batch = synthetic_batch(wl, 0)
     obj = workloads.CrossEntropy()
     if steps is None:                      # bounded sample: as many steps as fit the budget
         t1 = looper_port.time_steps(net, obj, opt, batch, steps=1, warmup=1, max_norm=1.0,
@@ -624,24 +929,31 @@ def cpu_port(budget_s: float, threads, as_line: bool, steps=None, warmup=1):
     sec = looper_port.time_steps(net, obj, opt, batch, steps=steps, warmup=warmup, max_norm=1.0,
                                  device="cpu")
     return {"value": round(BATCH / sec, 2), "unit": "samples/s", "cores": torch.get_num_threads(),
-            "kind": "port", "ms_per_step": round(sec * 1e3, 2),
+            "kind": "port", "ms_per_step": round(sec * 1e3, 2), "steps": steps,
             "sample": f"{steps} steps of the same workload (ResNet-18 bs=256, fp32) on CPU, "
                       f"os.cpu_count()={os.cpu_count()}"}
 
 
 def run_reference(args) -> dict:
+    """The reference arm: the reference's own arithmetic for this step (looper port: torch.optim
+    foreach=False + clip_grad_norm_) on this box's host cores, all threads, the same --steps
+    and --warmup and the same config as our arm.  One process whatever N is: the reference's
+    CPU path has no multi-GPU meaning, so at N > 1 the driver's ratio compares N GPUs with one
+    host (rank 0 runs it, the others exit)."""
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return {}
-    base = cpu_port(budget_s=0, threads=os.cpu_count(), as_line=True,
-                    steps=max(1, min(args.steps, 10)), warmup=max(1, min(args.warmup, 2)))
+    wl = WORKLOADS["resnet18"]
+    base = cpu_port(budget_s=0, threads=os.cpu_count(), steps=max(1, args.steps),
+                    warmup=max(1, min(args.warmup, 3)))
     return {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": "samples/s",
-            "n_gpus": args.gpus, "steps": max(1, min(args.steps, 10)), "warmup": args.warmup,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": base["ms_per_step"], "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "configs[1]: ResNet-18(num_classes=10), synthetic 3x32x32, "
-                                   "bs=256, AdamW+clip 1.0, fp32; reference arithmetic "
-                                   "(torch.optim foreach=False) on host CPU cores"},
+            "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
+            "config": {"workload": wl["label"], "global_batch": BATCH, "parallelism": "dp1",
+                       "params": 11181642},
+            "runs_on": "host CPU cores: reference arithmetic (torch.optim foreach=False + "
+                       "clip_grad_norm_) through oracle/looper_port.py; warm-up capped at 3 steps",
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "samples/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0}}
@@ -660,11 +972,13 @@ def main() -> None:
     ap.add_argument("--graph", type=int, default=None,
                     help="Module(graph=...): replay the training step from a CUDA graph (1) or "
                          "run it eagerly (0)")
+    ap.add_argument("--lean", action="store_true",
+                    help="headline legs only: no eager / torch_gpu / resnet50 / gpt2 objects")
+    ap.add_argument("--no-parity", action="store_true", help="skip the N > 1 parity_check")
+    ap.add_argument("--r50-steps", type=int, default=20, help="timed steps of the resnet50 object")
     ap.add_argument("--loader-workers", type=int, default=0,
                     help="DataLoader worker processes of the e2e leg (0 = load in-process)")
     args = ap.parse_args()
-    global WL
-    WL = WORKLOADS[args.workload]
     if args.graph is None:          # the host-bound headline workload replays its step from a graph
         args.graph = 1 if args.workload == "resnet18" else 0
     if args.impl == "reference":
@@ -672,7 +986,12 @@ def main() -> None:
         if out:
             print(json.dumps(out), flush=True)
         return
-    out = run_ours(args)
+    try:
+        out = run_ours(args)
+    except AssertionError as e:          # a parity check failed: say so and fail the run
+        if int(os.environ.get("RANK", 0)) == 0:
+            print(json.dumps({"parity_check": f"FAILED: {e!r}"}), flush=True)
+        raise
     if int(os.environ.get("RANK", 0)) == 0:
         print(json.dumps(out), flush=True)
     if dist.is_available() and dist.is_initialized():

@@ -160,6 +160,11 @@ class P2PGradSync(_BucketedSync):
         self._event = torch.cuda.Event()
         self.profile = False        # bench.py: bracket every exchange kernel with events
         self.timings: list = []     # (bucket bytes, start event, end event) on self.stream
+        # graph-captured steps: one external event pair around all buckets of the step, as
+        # event-record nodes of the graph (re-recorded by every replay); bench.py samples it
+        self.graph_ev = None
+        self.graph_ms: list = []
+        self.graph_bytes = 0
         ptrs, self.multicast_ptr, self._peers = map_arena(opt.arena, engine)
         # in-switch reduction moves ~G bytes per GPU instead of 2(W-1)/W * G: a win from W = 4
         want_mc = os.environ.get("ROCKET_B200_MULTICAST", "auto")
@@ -208,6 +213,41 @@ class P2PGradSync(_BucketedSync):
 
     def _wait(self) -> None:
         torch.cuda.current_stream(self.engine.device).wait_stream(self.stream)
+
+    def finish(self) -> bool:
+        gp = self.engine.graph_pass
+        if gp is None or gp.mode != "capture" or not self.graph_timing or self._finished:
+            return super().finish()
+        # being captured: every bucket is issued from here; bracket them on the side stream
+        t0 = torch.cuda.Event(enable_timing=True, external=True)
+        t1 = torch.cuda.Event(enable_timing=True, external=True)
+        self._event.record(torch.cuda.current_stream(self.engine.device))
+        self.stream.wait_event(self._event)
+        t0.record(self.stream)
+        before = self.bytes_reduced
+        for b in range(len(self.buckets)):
+            if not self._launched[b]:
+                self._launch(b)
+        t1.record(self.stream)
+        self.graph_ev, self.graph_bytes = (t0, t1), self.bytes_reduced - before
+        self._wait()
+        self._finished = True
+        return self.fused_norm
+
+    #: bench.py sets this to put the event pair above into captured steps
+    graph_timing = False
+
+    def sample_graph_events(self) -> None:
+        if self.graph_ev is None:
+            return
+        try:
+            s, e = self.graph_ev
+            if e.query():
+                dt = s.elapsed_time(e)
+                if 0.0 < dt < 50.0:              # a torn pair (replay in flight) is negative
+                    self.graph_ms.append(dt)
+        except Exception:
+            pass
 
     def remove(self) -> None:
         super().remove()

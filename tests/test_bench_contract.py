@@ -37,6 +37,12 @@ def test_reference_arm_prints_the_contract_line():
     assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
     assert line["cpu_baseline"]["value"] == line["value"] == line["e2e"]["value"]
     assert line["e2e"]["h2d_bytes_per_step"] == line["e2e"]["d2h_bytes_per_step"] == 0
+    # same --steps and the same config.workload string as our arm prints (the driver compares)
+    assert line["steps"] == 1 and line["cpu_baseline"]["steps"] == 1
+    sys.path.insert(0, str(ROOT))
+    import bench
+    assert line["config"]["workload"] == bench.WORKLOADS["resnet18"]["label"]
+    assert line["dtype"] == bench.WORKLOADS["resnet18"]["dtype"]
 
 
 def test_reference_arm_is_silent_on_other_ranks():

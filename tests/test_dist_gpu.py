@@ -156,83 +156,30 @@ def test_sharded_optimizer_step_equals_replicated_bitwise(case, world, tmp_path)
         assert n_state > 0
 
 
-def _allreduce_worker(rank: int, world: int, port: int, out_dir: str, arena_kind: str,
-                      multicast: bool) -> None:
+def _native_worker_setup(rank: int, world: int, port: int, extra_env=None):
     os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
-                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
-                      ROCKET_B200_ARENA=arena_kind)
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), **(extra_env or {}))
     root = Path(__file__).resolve().parent.parent
-    sys.path.insert(0, str(root))
+    for p in (str(root), str(root / "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
     import torch.distributed as dist
-    from rocket_b200 import _native as N
-    from rocket_b200.backend import NativeBackend, TensorSpec
-    from rocket_b200.comm import alloc_arena, map_arena
+    from rocket_b200.backend import NativeBackend
     dev = torch.device("cuda", rank)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev)
-    be = NativeBackend(dev)
-    sizes = [6, 10, 150, 4097, 48000, 1, 0, 123457, 3_000_001]       # awkward + multi-chunk
-    offs, total = [], 0
-    for n in sizes:
-        offs.append(total)
-        total += (n + 63) // 64 * 64
-    sig = N.RK_COMM_SIGNAL_BYTES
-    scratch = -(-be.scratch_bytes(sizes) // 256) * 256
-    arena = alloc_arena(sig + scratch + 4 * total, dev)
-    flat = arena[sig + scratch:].view(torch.float32)
-    views = [flat[o:o + n] for o, n in zip(offs, sizes)]
-    specs = [TensorSpec(p=torch.zeros(n, device=dev), g=v, m=None, v=None, group=0)
-             for n, v in zip(sizes, views)]
-    plan = be.make_plan(specs, scratch=arena[sig:sig + scratch])
+    return dist, NativeBackend(dev), dev
 
-    class Eng:
-        device, process_index, num_processes = dev, rank, world
-    ptrs, mc_ptr, peers = map_arena(arena, Eng)
-    if multicast and not mc_ptr:
-        dist.barrier()
-        dist.destroy_process_group()
+
+def _allreduce_worker(rank: int, world: int, port: int, out_dir: str, arena_kind: str,
+                      multicast: bool) -> None:
+    """The checks themselves live in tests/parity_checks.py (bench.py runs the same ones as its
+    `parity_check` at N > 1, where the driver's 8-GPU box can see them)."""
+    dist, be, dev = _native_worker_setup(rank, world, port, {"ROCKET_B200_ARENA": arena_kind})
+    import parity_checks
+    out = parity_checks.exchange_check(be, rank, world, dev, multicast)
+    if out is None:
         Path(out_dir, f"skipped_{rank}").write_text("no multicast support")
-        return
-    comm = be.comm_create(rank, world, ptrs, sig, mc_ptr)
-    dist.barrier()
-    stream = torch.cuda.current_stream().cuda_stream
-    half = plan.n_chunks_norm // 2
-    for it in range(3):                                 # epochs advance, nothing is reset
-        torch.manual_seed(100 * it + rank)
-        flat.zero_()                                    # padding between tensors stays zero
-        for v in views:
-            v.normal_(0, 1e-2)
-        want = flat.clone()
-        dist.all_reduce(want)
-        want /= world
-        torch.cuda.synchronize()
-        dist.barrier()
-        be.comm_allreduce_norm(comm, plan, half, plan.n_chunks_norm, 0, 0, stream, multicast)
-        be.comm_allreduce_norm(comm, plan, 0, half, 1, 0, stream, multicast)   # two buckets
-        norm = be.l2norm_finalize(plan, want_tensor_norms=True).clone()
-        torch.cuda.synchronize()
-        got = flat.clone()
-        # replicas bit-identical
-        gathered = [torch.empty_like(got) for _ in range(world)]
-        dist.all_gather(gathered, got)
-        for q in range(world):
-            assert torch.equal(gathered[q], gathered[0]), (it, q)
-        # value: sum_r(g_r) / W up to fp32 summation order (exact for W == 2)
-        if world == 2:
-            assert torch.equal(got, want)
-        else:
-            assert torch.allclose(got, want, rtol=2e-6, atol=1e-9)
-        # fused norm partials == the stand-alone norm kernel on the averaged gradients
-        ref_plan = be.make_plan(specs)
-        ref = be.l2norm(ref_plan, 1.0, want_tensor_norms=True)
-        torch.cuda.synchronize()
-        assert torch.equal(norm, ref), (float(norm), float(ref))
-        assert torch.equal(plan.tensor_norms, ref_plan.tensor_norms)
-    dist.barrier()
-    be.comm_destroy(comm)
-    del peers
-    torch.cuda.ipc_collect()
-    dist.barrier()
     dist.destroy_process_group()
 
 
@@ -253,132 +200,11 @@ def test_fused_allreduce_norm_kernel_against_nccl(world, path, tmp_path):
 
 def _sharded_step_worker(rank: int, world: int, port: int, out_dir: str, multicast: bool,
                          kind: str, compact: bool) -> None:
-    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
-                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    root = Path(__file__).resolve().parent.parent
-    sys.path.insert(0, str(root))
-    import torch.distributed as dist
-    from rocket_b200 import _native as N
-    from rocket_b200.backend import NativeBackend, TensorSpec
-    from rocket_b200.comm import alloc_arena, map_arena
-    dev = torch.device("cuda", rank)
-    torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", device_id=dev)
-    be = NativeBackend(dev)
-    sizes = [6, 10, 150, 4097, 48000, 1, 0, 123457, 3_000_001]
-    groups_of = [0, 1, 0, 1, 0, 1, 0, 1, 0]
-    offs, total = [], 0
-    for n in sizes:
-        offs.append(total)
-        total += (n + 63) // 64 * 64
-    sig = N.RK_COMM_SIGNAL_BYTES
-    scratch = -(-be.scratch_bytes(sizes) // 256) * 256
-    arena = alloc_arena(sig + scratch + 8 * total, dev)      # [signals|scratch|g|p]
-    flat_g = arena[sig + scratch:sig + scratch + 4 * total].view(torch.float32)
-    flat_p = arena[sig + scratch + 4 * total:].view(torch.float32)
-    sgd = kind == "sgd"
-    # moments: full-size per-tensor buffers in the plan, or this rank's compact shards
-    flat_m = None if compact else torch.zeros(total, device=dev)
-    flat_v = None if compact or sgd else torch.zeros(total, device=dev)
-    ref_p, ref_g, ref_m = (torch.zeros(total, device=dev) for _ in range(3))
-    ref_v = None if sgd else torch.zeros(total, device=dev)
-
-    def specs_of(p, g, m, v):
-        return [TensorSpec(p=p[o:o + n], g=g[o:o + n], m=None if m is None else m[o:o + n],
-                           v=None if v is None else v[o:o + n], group=gi)
-                for o, n, gi in zip(offs, sizes, groups_of)]
-    plan = be.make_plan(specs_of(flat_p, flat_g, flat_m, flat_v), scratch=arena[sig:sig + scratch])
-    ref_plan = be.make_plan(specs_of(ref_p, ref_g, ref_m, ref_v))
-
-    class Eng:
-        device, process_index, num_processes = dev, rank, world
-    ptrs, mc_ptr, peers = map_arena(arena, Eng)
-    if multicast and not mc_ptr:
-        dist.barrier()
-        dist.destroy_process_group()
+    dist, be, dev = _native_worker_setup(rank, world, port)
+    import parity_checks
+    out = parity_checks.sharded_step_check(be, rank, world, dev, multicast, kind, compact)
+    if out is None:
         Path(out_dir, f"skipped_{rank}").write_text("no multicast support")
-        return
-    comm = be.comm_create(rank, world, ptrs, sig, mc_ptr)
-    torch.manual_seed(7)
-    for o, n in zip(offs, sizes):
-        flat_p[o:o + n].normal_(0, 0.1)
-    ref_p.copy_(flat_p)
-    table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8, device=dev)
-    host_table = torch.zeros(N.RK_STEP_TABLE_BYTES, dtype=torch.uint8).pin_memory()
-    dist.barrier()
-    stream = torch.cuda.current_stream().cuda_stream
-    half = plan.n_chunks_norm // 2
-    chunk = plan.chunk_norm
-    rows = -(-plan.n_chunks_norm // world)
-    shard_m = torch.zeros(rows * chunk, device=dev) if compact else None
-    shard_v = torch.zeros(rows * chunk, device=dev) if compact and not sgd else None
-    owner = torch.zeros(total, dtype=torch.bool, device=dev)       # elements this rank owns
-    slot_of = torch.zeros(total, dtype=torch.int64, device=dev)    # ... and their shard position
-    for i, (o, n) in enumerate(zip(offs, sizes)):
-        e = torch.arange(n, device=dev)
-        c = e // chunk + int(plan.prefix_norm[i])
-        owner[o:o + n] = (c % world) == rank
-        slot_of[o:o + n] = (c // world) * chunk + e % chunk
-    for it in range(3):
-        torch.manual_seed(100 * it + rank)
-        flat_g.zero_()
-        for o, n in zip(offs, sizes):
-            flat_g[o:o + n].normal_(0, 1e-2)
-        if it == 1:
-            flat_g[offs[4]:offs[4] + 4000].zero_()        # zero gradients: the special values
-        mine = flat_g.clone()
-        if sgd:
-            groups = [dict(lr=0.05, momentum=0.9, dampening=0.0, weight_decay=1e-4,
-                           nesterov=gi == 1, first_step=it == 0, skip=False) for gi in range(2)]
-        else:
-            groups = [dict(lr=1e-3 * (gi + 1), beta1=0.9, beta2=0.999, eps=1e-8,
-                           weight_decay=0.01 * gi, step=it + 1, decoupled=True, skip=False)
-                      for gi in range(2)]
-        max_norm = 0.0 if it == 2 else 0.05
-        # replicated arm: fused all-reduce, then the ordinary step kernel on private copies
-        torch.cuda.synchronize(); dist.barrier()
-        be.comm_allreduce_norm(comm, plan, half, plan.n_chunks_norm, 0, 0, stream, multicast)
-        be.comm_allreduce_norm(comm, plan, 0, half, 1, 0, stream, multicast)
-        norm_a = be.l2norm_finalize(plan).clone()
-        ref_g.copy_(flat_g)
-        (be.sgd_step if sgd else be.adam_step)(ref_plan, groups, norm_a if max_norm else None,
-                                               max_norm, 1.0, True)
-        torch.cuda.synchronize(); dist.barrier()
-        # sharded arm on the same inputs
-        flat_g.copy_(mine)
-        torch.cuda.synchronize(); dist.barrier()
-        be.comm_reduce_scatter_norm(comm, plan, half, plan.n_chunks_norm, 0, 0, stream, multicast)
-        be.comm_reduce_scatter_norm(comm, plan, 0, half, 1, 0, stream, multicast)
-        norm_b = be.l2norm_finalize(plan)
-        be.step_table_write(kind, groups, host_table)
-        table.copy_(host_table, non_blocking=True)
-        be.comm_sharded_step(comm, plan, kind, table.data_ptr(), norm_b if max_norm else None,
-                             max_norm, 0, multicast, shard_m, shard_v)
-        torch.cuda.synchronize()
-        assert torch.equal(norm_a, norm_b), (it, float(norm_a), float(norm_b))
-        assert torch.equal(flat_p.view(torch.int32), ref_p.view(torch.int32)), \
-            (it, int((flat_p != ref_p).sum()))
-        assert not flat_g.any(), it
-        if compact:
-            pairs = [(shard_m, ref_m)] + ([] if sgd else [(shard_v, ref_v)])
-            for shard, ref_s in pairs:
-                # owned elements sit in slot c // W of the shard; every other slot stays zero
-                assert torch.equal(shard[slot_of[owner]].view(torch.int32),
-                                   ref_s[owner].view(torch.int32)), it
-                untouched = torch.ones_like(shard, dtype=torch.bool)
-                untouched[slot_of[owner]] = False
-                assert not shard[untouched].any(), it
-        else:
-            pairs = [(flat_m, ref_m)] + ([] if sgd else [(flat_v, ref_v)])
-            for mine_s, ref_s in pairs:
-                assert torch.equal(mine_s[owner].view(torch.int32),
-                                   ref_s[owner].view(torch.int32)), it
-                assert not mine_s[~owner].any(), it       # other ranks' chunks are never touched
-    dist.barrier()
-    be.comm_destroy(comm)
-    del peers
-    torch.cuda.ipc_collect()
-    dist.barrier()
     dist.destroy_process_group()
 
 
