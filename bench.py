@@ -189,13 +189,15 @@ WORKLOADS = {
 }
 
 
-def set_precision(wl) -> None:
+def set_precision(wl, tf32_conv: bool = False) -> None:
     """The line whose dtype says f32 computes in true fp32: TF32 off for convolutions and
-    matmuls, which is also what every parity test runs (tests/test_engine_gpu.py).  The bf16
+    matmuls, which is what every parity test runs (tests/test_engine_gpu.py) and what the
+    reference arm's host CPU computes.  (torch's own default leaves cuDNN TF32 convolutions
+    on; `tf32_conv=True` is that setting, reported separately as `tf32_conv`.)  The bf16
     workloads autocast; whatever stays fp32 there keeps torch's defaults."""
-    fp32 = wl["mixed_precision"] is None
+    fp32 = wl["mixed_precision"] is None and not tf32_conv
     torch.backends.cudnn.allow_tf32 = not fp32
-    torch.backends.cuda.matmul.allow_tf32 = not fp32
+    torch.backends.cuda.matmul.allow_tf32 = wl["mixed_precision"] is not None
     torch.backends.cudnn.benchmark = True
 
 
@@ -214,7 +216,8 @@ def env_ranks():
             int(os.environ.get("LOCAL_RANK", 0)))
 
 
-def run_capsule(wl, *, graph: bool, steps: int, warmup: int, e2e: bool, loader_workers: int = 0):
+def run_capsule(wl, *, graph: bool, steps: int, warmup: int, e2e: bool, loader_workers: int = 0,
+                tf32_conv: bool = False):
     """One Launcher.launch() of the capsule graph on `wl`: `warmup` untimed iterations, then
     exactly `steps` timed ones between two barrier + device-sync fences (CUDA events, max over
     ranks).  e2e=False: one batch resident in HBM; e2e=True: host batches through
@@ -234,7 +237,7 @@ def run_capsule(wl, *, graph: bool, steps: int, warmup: int, e2e: bool, loader_w
         # captures: with a short --warmup the capture would land inside the timed region.
         # Extra untimed steps keep it out; the line reports the warm-up actually done.
         W = max(W, (rk.Module.GRAPH_WARMUP + 2) * accum)
-    set_precision(wl)
+    set_precision(wl, tf32_conv)
 
     class TimedBackend(NativeBackend):
         """Brackets each engine kernel launch with CUDA events on its own stream.  While a
@@ -441,9 +444,10 @@ def run_capsule(wl, *, graph: bool, steps: int, warmup: int, e2e: bool, loader_w
            "exchange_graph_bytes": getattr(probe.sync, "graph_bytes", 0)}
     if world > 1:
         import parity_checks
+        # parameters only: BatchNorm running statistics are rank-local between the broadcasts
+        # in front of each forward (as under DDP), and do not feed the training-mode forward
         res["replicas_identical"] = parity_checks.replicas_identical(
-            params + [b for b in net.buffers() if b.dtype.is_floating_point],
-            torch.device("cuda", local))
+            params, torch.device("cuda", local))
     if e2e:
         sample_bytes = 8 * wl["shape"][0] if wl.get("tokens") else \
             4 * wl["shape"][0] * wl["shape"][1] * wl["shape"][2]
@@ -683,6 +687,20 @@ def run_ours(args) -> dict:
             if xe:
                 out["eager"]["exchange"] = xe
         out["torch_gpu"] = torch_gpu_baseline(wl, steps=min(K, 50), warmup=max(5, args.warmup // 2))
+        # torch's default precision for this model (cuDNN convolutions in TF32): not the
+        # parity-tested setting and not what the CPU reference arm computes, so not the headline
+        tf = run_capsule(wl, graph=args.graph, steps=K, warmup=args.warmup, e2e=False,
+                         tf32_conv=True)
+        tfe = run_capsule(wl, graph=args.graph, steps=K, warmup=args.warmup, e2e=True,
+                          loader_workers=args.loader_workers, tf32_conv=True)
+        k2t = statistics.mean(tf["step_ms"]) if tf["step_ms"] else float("nan")
+        out["tf32_conv"] = {
+            "dtype": "f32 params and optimizer / TF32 cuDNN convolutions (torch default)",
+            "value": round(tf["value"], 1), "unit": "samples/s",
+            "ms_per_step": round(tf["ms_per_step"], 4),
+            "e2e": {"value": round(tfe["value"], 1), "ms_per_step": round(tfe["ms_per_step"], 4)},
+            "step_kernel_ms": round(k2t, 5),
+            "step_kernel_gbs": round(algo * tf["n_params"] / (k2t * 1e-3) / 1e9, 1)}
         # configs[2]: the workload the north_star puts the >= 7x scaling target on
         w50 = WORKLOADS["resnet50"]
         r50 = run_capsule(w50, graph=False, steps=args.r50_steps, warmup=5, e2e=False)
