@@ -134,9 +134,11 @@ int rk_l2norm_multi(const void* plan_host, const void* plan_dev, float grad_scal
  *   - Tensor lists whose plan needs more scratch than that (rk_plan_query's
  *     scratch_bytes; roughly 8 bytes per norm chunk + 4 per tensor, i.e. beyond ~100K
  *     tensors) are refused with RK_ERR_TOO_LARGE and a message; nothing is launched.
- *   - The first call on each device looks up the array's device address (that device must
- *     be current, as for every call here).  Make that first call before starting any
- *     stream capture.
+ *   - Every call looks the array's device address up afresh (the device the call is for must
+ *     be current, and `stream` must belong to it: neither is checked), so the entry point
+ *     keeps working after cudaDeviceReset or a re-created primary context.  The first call on
+ *     each device additionally does one-time set-up (it loads the kernel and sizes its grid):
+ *     make that first call before starting any stream capture.
  *   - All calls on a device share the one array.  It keeps the previous call's contents;
  *     the entry point clears the part that must start at zero itself.  Two calls whose
  *     kernels can overlap on the GPU (different streams, or different host threads without

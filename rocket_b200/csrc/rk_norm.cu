@@ -283,35 +283,37 @@ extern "C" int rk_l2norm_multi(const void* plan_host, const void* plan_dev, floa
 // ---- the same norm for callers that have no scratch buffer to give ---------------------
 // Scratch for rk_l2norm_multi_static lives in this module's own device image: one array per
 // GPU that loads the library, held until the process exits.  In host code `g_static_scratch`
-// is only a stand-in for the symbol, not a device address; the address is looked up once per
-// device with cudaGetSymbolAddress (with that device current) and handed to the kernel.
+// is only a stand-in for the symbol, not a device address; the address is looked up with
+// cudaGetSymbolAddress (with the target device current) and handed to the kernel.
 static __device__ __align__(256) unsigned char g_static_scratch[RK_STATIC_SCRATCH_BYTES];
 
 #define RK_MAX_DEVICES 64
 static std::mutex g_static_mu;
-static void* g_static_ptr[RK_MAX_DEVICES];   // device address of g_static_scratch, per device
-static int g_static_resident[RK_MAX_DEVICES];  // persistent grid size, per device
+static int g_static_resident[RK_MAX_DEVICES];  // persistent grid size, per device (set-up, once)
 
+// The array's device address is looked up on EVERY call (a host-side table lookup in the CUDA
+// runtime: no allocation, no stream work).  Caching it per device ordinal would hand a dangling
+// pointer to the kernel after cudaDeviceReset or any other tear-down and re-creation of the
+// device's primary context; the fresh lookup follows the context that is current now.
 static int static_setup_current_device(void** scratch, int* resident) {
   int dev = -1;
   RK_CUDA(cudaGetDevice(&dev));
   RK_REQUIRE(dev >= 0 && dev < RK_MAX_DEVICES, RK_ERR_UNSUPPORTED,
              "rk_l2norm_multi_static: device ordinal %d not supported (max %d)", dev,
              RK_MAX_DEVICES - 1);
+  void* p = nullptr;
+  RK_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+  RK_REQUIRE(p != nullptr, RK_ERR_STATE, "cudaGetSymbolAddress returned a null address");
   std::lock_guard<std::mutex> lk(g_static_mu);
-  if (g_static_ptr[dev] == nullptr) {
-    void* p = nullptr;
-    RK_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
-    RK_REQUIRE(p != nullptr, RK_ERR_STATE, "cudaGetSymbolAddress returned a null address");
+  if (g_static_resident[dev] == 0) {
     int sms = 0, per_sm = 0;
     RK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     RK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_l2norm_kernel,
                                                           NORM_THREADS, 0));
     RK_REQUIRE(sms > 0 && per_sm > 0, RK_ERR_STATE, "norm kernel does not fit on an SM");
     g_static_resident[dev] = sms * per_sm;
-    g_static_ptr[dev] = p;
   }
-  *scratch = g_static_ptr[dev];
+  *scratch = p;
   *resident = g_static_resident[dev];
   return 0;
 }

@@ -19,7 +19,6 @@ from __future__ import annotations
 
 import contextlib
 import os
-import pickle
 
 import torch
 import torch.distributed as dist
@@ -466,35 +465,67 @@ class Engine:
                              f"load_state_dict(): {[type(o).__name__ for o in bad]}")
         self._custom_objects.extend(objects)
 
+    # File names and serializers follow accelerate's `save_state` / `load_state` layout, so that
+    # a checkpoint directory means the same to either library [accelerate >= 0.34, from memory:
+    # checkpointing.py save_accelerator_state / load_accelerator_state; the package is not on
+    # this image, so the layout is restated, not verified against an install]:
+    #   model.safetensors, model_1.safetensors ...   (read side also accepts pytorch_model*.bin)
+    #   optimizer.bin, optimizer_1.bin ...           torch.save of the torch-format state_dict
+    #   scheduler.bin ...                            torch.save
+    #   scaler.pt                                    GradScaler's state_dict (fp16 only)
+    #   random_states_<rank>.pkl                     torch.save of python / numpy / torch / cuda RNG
+    #   custom_checkpoint_<i>.pkl                    torch.save of each registered object's state
+    @staticmethod
+    def _numbered(stem: str, i: int, ext: str) -> str:
+        return f"{stem}{'' if i == 0 else f'_{i}'}.{ext}"
+
+    @staticmethod
+    def _model_tensors(model: torch.nn.Module) -> dict:
+        """state_dict as safetensors wants it: host copies, one name per aliased tensor (tied
+        weights are written once, under their first name, like safetensors' save_model)."""
+        out, seen = {}, set()
+        for name, t in model.state_dict().items():
+            key = (t.data_ptr(), tuple(t.shape), t.dtype) if t.numel() else (name,)
+            if key in seen:
+                continue
+            seen.add(key)
+            out[name] = t.detach().cpu().contiguous()
+        return out
+
     def save_state(self, output_dir: str | None = None, **_) -> str:
         if output_dir is None:
             if self.project_dir is None:
                 raise ValueError("save_state needs an output_dir or a project_dir")
             output_dir = os.path.join(self.project_dir, "checkpoints")
+        from safetensors.torch import save_file
+        # collective parts first (a sharded optimizer gathers its moments): every rank gets here
         states = {
-            "models": [m.state_dict() for m in self._models],
             "optimizers": [o.state_dict() for o in self._optimizers],
             "schedulers": [s.state_dict() for s in self._schedulers],
             "custom": [c.state_dict() for c in self._custom_objects],
         }
+        os.makedirs(output_dir, exist_ok=True)
         if self.is_main_process:
-            os.makedirs(output_dir, exist_ok=True)
-            for i, sd in enumerate(states["models"]):
-                torch.save(sd, os.path.join(output_dir, f"model_{i}.pt"))
+            for i, m in enumerate(self._models):
+                save_file(self._model_tensors(m),
+                          os.path.join(output_dir, self._numbered("model", i, "safetensors")))
             for i, sd in enumerate(states["optimizers"]):
-                torch.save(sd, os.path.join(output_dir, f"optimizer_{i}.pt"))
+                torch.save(sd, os.path.join(output_dir, self._numbered("optimizer", i, "bin")))
             for i, sd in enumerate(states["schedulers"]):
-                torch.save(sd, os.path.join(output_dir, f"scheduler_{i}.pt"))
+                torch.save(sd, os.path.join(output_dir, self._numbered("scheduler", i, "bin")))
             for i, sd in enumerate(states["custom"]):
-                with open(os.path.join(output_dir, f"custom_checkpoint_{i}.pkl"), "wb") as f:
-                    pickle.dump(sd, f)
+                torch.save(sd, os.path.join(output_dir, f"custom_checkpoint_{i}.pkl"))
             if self.scaler is not None:          # accelerate: scaler.pt, GradScaler's format
                 torch.save(self.scaler.state_dict(), os.path.join(output_dir, "scaler.pt"))
-        os.makedirs(output_dir, exist_ok=True)
-        rng = {"torch": torch.get_rng_state()}
+        import random
+
+        import numpy as np
+        rng = {"step": self.step, "random_state": random.getstate(),
+               "numpy_random_seed": np.random.get_state(),
+               "torch_manual_seed": torch.get_rng_state()}
         if self.device.type == "cuda":
-            rng["cuda"] = torch.cuda.get_rng_state(self.device)
-        torch.save(rng, os.path.join(output_dir, f"random_states_{self.process_index}.pt"))
+            rng["torch_cuda_manual_seed"] = torch.cuda.get_rng_state_all()
+        torch.save(rng, os.path.join(output_dir, f"random_states_{self.process_index}.pkl"))
         self.wait_for_everyone()
         return output_dir
 
@@ -503,24 +534,45 @@ class Engine:
             raise RuntimeError(f"checkpoint directory {input_dir!r} does not exist")
         dev = self.device
         for i, m in enumerate(self._models):
-            m.load_state_dict(torch.load(os.path.join(input_dir, f"model_{i}.pt"),
-                                         map_location=dev))
+            safe = os.path.join(input_dir, self._numbered("model", i, "safetensors"))
+            if os.path.exists(safe):
+                from safetensors.torch import load_file
+                sd = load_file(safe, device=str(dev))
+                missing, unexpected = m.load_state_dict(sd, strict=False)
+                # names left out on purpose: aliases of a tensor that was written
+                written = {t.data_ptr() for k, t in m.state_dict().items() if k in sd}
+                lost = [k for k in missing if m.state_dict()[k].data_ptr() not in written]
+                if lost or unexpected:
+                    raise RuntimeError(f"{safe}: missing {lost}, unexpected {list(unexpected)}")
+            else:                                 # accelerate with safe_serialization=False
+                m.load_state_dict(torch.load(
+                    os.path.join(input_dir, self._numbered("pytorch_model", i, "bin")),
+                    map_location=dev, weights_only=True))
         for i, o in enumerate(self._optimizers):
-            o.load_state_dict(torch.load(os.path.join(input_dir, f"optimizer_{i}.pt"),
-                                         map_location=dev))
+            o.load_state_dict(torch.load(
+                os.path.join(input_dir, self._numbered("optimizer", i, "bin")),
+                map_location=dev, weights_only=True))
         for i, s in enumerate(self._schedulers):
-            s.load_state_dict(torch.load(os.path.join(input_dir, f"scheduler_{i}.pt")))
+            s.load_state_dict(torch.load(
+                os.path.join(input_dir, self._numbered("scheduler", i, "bin")),
+                weights_only=False))              # scheduler state may hold plain objects
         for i, c in enumerate(self._custom_objects):
-            with open(os.path.join(input_dir, f"custom_checkpoint_{i}.pkl"), "rb") as f:
-                c.load_state_dict(pickle.load(f))
+            c.load_state_dict(torch.load(os.path.join(input_dir, f"custom_checkpoint_{i}.pkl"),
+                                         map_location="cpu", weights_only=False))
         if self.scaler is not None:
             self.scaler.load_state_dict(torch.load(os.path.join(input_dir, "scaler.pt")))
-        rng_path = os.path.join(input_dir, f"random_states_{self.process_index}.pt")
+        rng_path = os.path.join(input_dir, f"random_states_{self.process_index}.pkl")
         if os.path.exists(rng_path):
-            rng = torch.load(rng_path)
-            torch.set_rng_state(rng["torch"])
-            if "cuda" in rng and dev.type == "cuda":
-                torch.cuda.set_rng_state(rng["cuda"], dev)
+            import random
+
+            import numpy as np
+            rng = torch.load(rng_path, weights_only=False)
+            self.step = rng.get("step", self.step)
+            random.setstate(rng["random_state"])
+            np.random.set_state(rng["numpy_random_seed"])
+            torch.set_rng_state(rng["torch_manual_seed"])
+            if "torch_cuda_manual_seed" in rng and dev.type == "cuda":
+                torch.cuda.set_rng_state_all(rng["torch_cuda_manual_seed"])
 
     # ---- trackers (reference tracker.py:89-105) -----------------------------------------------------------------
     def get_tracker(self, name: str, unwrap: bool = False):

@@ -76,9 +76,12 @@ class EngineOptimizer:
         self._group_of: list[int] = []
         self._offsets: list[int] = []
         off = 0
+        self._frozen: list[torch.nn.Parameter] = []     # requires_grad=False at prepare time
+        self._n_group_params = sum(len(g["params"]) for g in self.optimizer.param_groups)
         for gi, group in enumerate(self.optimizer.param_groups):
             for p in group["params"]:
                 if not p.requires_grad:
+                    self._frozen.append(p)
                     continue
                 if p.dtype != torch.float32:
                     raise NotImplementedError(
@@ -140,7 +143,17 @@ class EngineOptimizer:
                                      if self.flat_v is not None else None)
         self._grad_ptr = [v.data_ptr() for v in self._views_g]
         self._adopted = [False] * len(self._params)      # grad lives in flat_g
+        # torch keeps Adam's `step` (and SGD's "no momentum buffer yet") per PARAMETER
+        # ($TORCH/optim/adam.py:168-175,414; sgd.py:359-365): a parameter whose first gradient
+        # arrives after its group-mates' gets its own bias correction.  Here: steps taken per
+        # group, and per parameter how many of them it missed before its gradient first showed
+        # up; parameters of one group with the same lag share one row of the kernels'
+        # constant table (normally: one row per group).
         self._group_step = [0] * len(self.optimizer.param_groups)
+        self._lag = [0] * len(self._params)
+        self._lag_known = [False] * len(self._params)    # taken from imported optimizer state
+        self._rows: list[tuple[int, int]] = []           # (param group, lag) per table row
+        self._row_of = [0] * len(self._params)
         self._plan = None
         self._table_ring = None
         self._dev_table = torch.zeros(4096, dtype=torch.uint8, device=dev)
@@ -163,6 +176,8 @@ class EngineOptimizer:
             gi = self._group_of[i]
             if "step" in st:
                 self._group_step[gi] = max(self._group_step[gi], int(float(st["step"])))
+                self._lag[i] = -int(float(st["step"]))    # fixed up below, once the max is known
+                self._lag_known[i] = True
             if self._kind == "sgd":
                 buf = st.get("momentum_buffer")
                 if buf is not None and self._needs_m:
@@ -172,6 +187,7 @@ class EngineOptimizer:
                         self._views_m[i].copy_(buf)
                         st["momentum_buffer"] = self._views_m[i]
                     self._group_step[gi] = max(self._group_step[gi], 1)
+                    self._lag_known[i] = True
             elif "exp_avg" in st:
                 if self.sharded:
                     self._scatter(i, st["exp_avg"], self.shard_m)
@@ -180,6 +196,11 @@ class EngineOptimizer:
                     self._views_m[i].copy_(st["exp_avg"])
                     self._views_v[i].copy_(st["exp_avg_sq"])
                     st["exp_avg"], st["exp_avg_sq"] = self._views_m[i], self._views_v[i]
+        for i in range(len(self._params)):
+            if self._lag[i] < 0:                 # had a `step`: lag = group's steps - its own
+                self._lag[i] += self._group_step[self._group_of[i]]
+            elif self._lag_known[i] and self._kind == "sgd":
+                self._lag[i] = 0                 # has a momentum buffer: not its first step
 
     # ---- sharded step: compact moment shards ---------------------------------------------------
     # Norm chunk c (global index over all tensors, plan.prefix_norm) belongs to rank c % W, as
@@ -352,29 +373,54 @@ class EngineOptimizer:
         scaler = getattr(self.engine, "scaler", None)
         return scale * scaler.inv_scale if scaler is not None else scale
 
+    def _check_param_set(self) -> None:
+        """The flat layout is fixed at prepare time; changes torch.optim would pick up silently
+        are refused loudly instead of being ignored."""
+        if sum(len(g["params"]) for g in self.optimizer.param_groups) != self._n_group_params:
+            raise NotImplementedError(
+                "param groups changed after prepare (add_param_group): prepare a new optimizer")
+        if self._frozen and any(p.requires_grad for p in self._frozen):
+            raise NotImplementedError(
+                "a parameter that had requires_grad=False when the optimizer was prepared now "
+                "requires grad: it has no slot in the flat layout; prepare a new optimizer")
+
+    def _assign_rows(self) -> None:
+        """One table row per (param group, lag) among the adopted parameters."""
+        keys = sorted({(self._group_of[i], self._lag[i])
+                       for i in range(len(self._params)) if self._adopted[i]})
+        if len(keys) > 64:
+            raise NotImplementedError(
+                f"{len(keys)} distinct (param group, first-gradient step) combinations; the "
+                "kernels' constant table holds 64 (RK_MAX_GROUPS)")
+        index = {k: r for r, k in enumerate(keys)}
+        self._rows = keys
+        for i in range(len(self._params)):
+            self._row_of[i] = index.get((self._group_of[i], self._lag[i]), 0)
+
     def _step_groups(self) -> list[dict]:
-        """This step's hyper-parameters per param group (advances the step counters)."""
-        active = set(self._group_of[i] for i in range(len(self._params)) if self._adopted[i])
-        groups = []
-        for gi, g in enumerate(self.optimizer.param_groups):
-            skip = gi not in active
-            if not skip:
-                self._group_step[gi] += 1
+        """This step's hyper-parameters per table row (advances the step counters)."""
+        active = set(gi for gi, _ in self._rows)
+        for gi in active:
+            self._group_step[gi] += 1
+        rows = []
+        for gi, lag in self._rows:
+            g = self.optimizer.param_groups[gi]
+            step = self._group_step[gi] - lag            # this row's parameters' own count
             if self._kind == "sgd":
-                groups.append(dict(lr=float(g["lr"]), momentum=float(g["momentum"]),
-                                   dampening=float(g["dampening"]),
-                                   weight_decay=float(g["weight_decay"]),
-                                   nesterov=bool(g["nesterov"]),
-                                   first_step=self._group_step[gi] <= 1, skip=skip))
+                rows.append(dict(lr=float(g["lr"]), momentum=float(g["momentum"]),
+                                 dampening=float(g["dampening"]),
+                                 weight_decay=float(g["weight_decay"]),
+                                 nesterov=bool(g["nesterov"]),
+                                 first_step=step <= 1, skip=False))
             else:
-                groups.append(dict(lr=float(g["lr"]), beta1=float(g["betas"][0]),
-                                   beta2=float(g["betas"][1]), eps=float(g["eps"]),
-                                   weight_decay=float(g["weight_decay"]),
-                                   step=max(self._group_step[gi], 1),
-                                   decoupled=self._kind == "adamw"
-                                   or bool(g.get("decoupled_weight_decay", False)),
-                                   skip=skip))
-        return groups
+                rows.append(dict(lr=float(g["lr"]), beta1=float(g["betas"][0]),
+                                 beta2=float(g["betas"][1]), eps=float(g["eps"]),
+                                 weight_decay=float(g["weight_decay"]),
+                                 step=max(step, 1),
+                                 decoupled=self._kind == "adamw"
+                                 or bool(g.get("decoupled_weight_decay", False)),
+                                 skip=False))
+        return rows
 
     _TABLE_SLOTS = 32
 
@@ -405,6 +451,7 @@ class EngineOptimizer:
         code replaced ``p.grad``): copy the gradient into its flat view and re-point
         ``p.grad`` there, so later backward passes accumulate in place.
         """
+        self._check_param_set()
         changed = False
         for i, p in enumerate(self._params):
             g = p.grad
@@ -421,8 +468,12 @@ class EngineOptimizer:
                 p.grad = self._views_g[i]
             if not self._adopted[i]:
                 self._adopted[i] = True
+                if not self._lag_known[i]:
+                    self._lag[i] = self._group_step[self._group_of[i]]   # steps it did not take
+                    self._lag_known[i] = True
                 changed = True
         if changed:
+            self._assign_rows()
             self._plan = None
 
     def _get_plan(self):
@@ -432,7 +483,7 @@ class EngineOptimizer:
                                 if self._views_m[i] is not None else None,
                                 v=self._views_v[i].reshape(-1)
                                 if self._views_v[i] is not None else None,
-                                group=self._group_of[i], skip=not self._adopted[i])
+                                group=self._row_of[i], skip=not self._adopted[i])
                      for i in range(len(self._params))]
             if self._scratch_view is not None:
                 self._plan = self.engine.backend.make_plan(specs, scratch=self._scratch_view)
@@ -453,8 +504,8 @@ class EngineOptimizer:
         for i, p in enumerate(self._params):
             if not self._adopted[i]:
                 continue
-            step = self._group_step[self._group_of[i]]
-            if step == 0:
+            step = self._group_step[self._group_of[i]] - self._lag[i]
+            if step <= 0:
                 continue
             st = self.optimizer.state[p]
             if self._kind == "sgd":
@@ -470,6 +521,8 @@ class EngineOptimizer:
     def load_state_dict(self, state_dict: dict) -> None:
         self.optimizer.load_state_dict(state_dict)
         self._group_step = [0] * len(self.optimizer.param_groups)
+        self._lag = [0] * len(self._params)
+        self._lag_known = [False] * len(self._params)
         with torch.no_grad():
             self._import_state()
             for i, p in enumerate(self._params):
@@ -479,7 +532,12 @@ class EngineOptimizer:
                         if p.grad is None or p.grad.data_ptr() != self._grad_ptr[i]:
                             self._views_g[i].zero_()
                             p.grad = self._views_g[i]
-                        self._plan = None
+                elif self._adopted[i]:
+                    # adopted here but without state in the checkpoint: it starts counting now
+                    self._lag[i] = self._group_step[self._group_of[i]]
+                    self._lag_known[i] = True
+            self._assign_rows()
+            self._plan = None
 
     # ---- introspection used by bench / tests ---------------------------------------------------------------
     @property

@@ -127,37 +127,73 @@ def _unflatten(template, leaves: list) -> Any:
     return template
 
 
+class _Ring:
+    """One generation of the staging rings: the pinned and device allocations plus the native
+    handle (copy stream, events, worker thread) that was created over them.  A ring that has
+    been superseded by a larger one stays alive until every batch submitted to it has been
+    collected and released."""
+
+    def __init__(self, lib, device: torch.device, slot_bytes: int, slots: int, threads: int):
+        self.lib, self.device = lib, device
+        self.slot_bytes, self.slots = slot_bytes, slots
+        total = slot_bytes * slots
+        self.pinned = torch.empty(total, dtype=torch.uint8).pin_memory()
+        self.dev = torch.empty(total, dtype=torch.uint8, device=device)
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(device):
+            N.check(lib.rk_stage_create(ctypes.byref(handle), self.pinned.data_ptr(),
+                                        self.dev.data_ptr(), slot_bytes, slots, threads),
+                    "rk_stage_create")
+        self.handle = handle
+        self.next = 0
+        self.outstanding = 0        # batches submitted and not yet released
+        self.retired = False
+
+    def destroy(self) -> None:
+        if self.handle is not None:
+            torch.cuda.synchronize(self.device)
+            self.lib.rk_stage_destroy(self.handle)
+            self.handle = None
+        self.pinned = None
+        # self.dev is dropped with the last batch view that still refers to it
+
+
 class PinnedRingStager:
     """Python face of ``rk_stage_*``: owns the pinned and device rings (torch allocations,
-    passed to the library as raw pointers) and turns batches into device views."""
+    passed to the library as raw pointers) and turns batches into device views.
+
+    The rings grow when a batch does not fit (variable-size batches, e.g. pad-to-longest).
+    Batches already submitted keep the ring they were submitted to: a ticket carries its ring,
+    so growing never invalidates a pending batch (the loader always has one in flight)."""
 
     def __init__(self, device: torch.device, slots: int = 3, copy_threads: int = 4):
         self.lib = N.load()
         self.device = device
         self.slots = slots
         self.copy_threads = copy_threads
-        self.slot_bytes = 0
-        self._handle = None
-        self._pinned = self._dev = None
-        self._next = 0
+        self._ring: _Ring | None = None
+        self._old: list[_Ring] = []
         self.h2d_bytes = 0
         self.batches = 0
+        self.rings_created = 0
+
+    @property
+    def slot_bytes(self) -> int:
+        return self._ring.slot_bytes if self._ring is not None else 0
 
     def _ensure(self, need: int) -> None:
-        if need <= self.slot_bytes:
+        if self._ring is not None and need <= self._ring.slot_bytes:
             return
-        self.close()
-        self.slot_bytes = max(1 << 20, -(-int(need * 1.25) // (1 << 20)) * (1 << 20))
-        total = self.slot_bytes * self.slots
-        self._pinned = torch.empty(total, dtype=torch.uint8).pin_memory()
-        self._dev = torch.empty(total, dtype=torch.uint8, device=self.device)
-        handle = ctypes.c_void_p()
-        with torch.cuda.device(self.device):
-            N.check(self.lib.rk_stage_create(ctypes.byref(handle), self._pinned.data_ptr(),
-                                             self._dev.data_ptr(), self.slot_bytes, self.slots,
-                                             self.copy_threads), "rk_stage_create")
-        self._handle = handle
-        self._next = 0
+        old = self._ring
+        slot_bytes = max(1 << 20, -(-int(need * 1.25) // (1 << 20)) * (1 << 20))
+        self._ring = _Ring(self.lib, self.device, slot_bytes, self.slots, self.copy_threads)
+        self.rings_created += 1
+        if old is not None:
+            old.retired = True
+            if old.outstanding == 0:
+                old.destroy()
+            else:
+                self._old.append(old)
 
     def submit(self, batch):
         """Start staging ``batch``. Returns an opaque ticket for :meth:`collect`."""
@@ -170,50 +206,57 @@ class PinnedRingStager:
             nbytes = t.numel() * t.element_size()
             leaves.append(_Leaf(off, t.dtype, t.shape, nbytes))
             off = -(-(off + nbytes) // _SEG_ALIGN) * _SEG_ALIGN
-        if off > self.slot_bytes:
-            torch.cuda.current_stream(self.device).synchronize()
-            self._ensure(off)
-        slot = self._next
-        self._next = (self._next + 1) % self.slots
+        self._ensure(off)
+        ring = self._ring
+        slot = ring.next
+        ring.next = (ring.next + 1) % ring.slots
         n = len(tensors)
         src = (ctypes.c_void_p * n)(*[t.data_ptr() for t in tensors])
         offs = (ctypes.c_size_t * n)(*[lf.offset for lf in leaves])
         sizes = (ctypes.c_size_t * n)(*[lf.nbytes for lf in leaves])
         ticket = ctypes.c_uint64()
-        N.check(self.lib.rk_stage_submit(self._handle, slot, src, offs, sizes, n,
+        N.check(self.lib.rk_stage_submit(ring.handle, slot, src, offs, sizes, n,
                                          ctypes.byref(ticket)), "rk_stage_submit")
+        ring.outstanding += 1
         self.h2d_bytes += sum(lf.nbytes for lf in leaves)
         self.batches += 1
         # `tensors` is kept in the ticket so the host memory outlives the worker's memcpy
-        return (ticket.value, slot, template, leaves, tensors)
+        return (ticket.value, (ring, slot), template, leaves, tensors)
 
     def collect(self, pending):
-        """Make the staged batch visible to the current stream and build the device views."""
-        ticket, slot, template, leaves, _keepalive = pending
+        """Make the staged batch visible to the current stream and build the device views.
+        Returns the batch and the token :meth:`release` takes."""
+        ticket, where, template, leaves, _keepalive = pending
         if ticket is None:
             return template, None
+        ring, slot = where
         stream = torch.cuda.current_stream(self.device).cuda_stream
-        N.check(self.lib.rk_stage_wait(self._handle, ticket, stream), "rk_stage_wait")
-        base = slot * self.slot_bytes
+        N.check(self.lib.rk_stage_wait(ring.handle, ticket, stream), "rk_stage_wait")
+        base = slot * ring.slot_bytes
         out = []
         for lf in leaves:
-            raw = self._dev[base + lf.offset: base + lf.offset + lf.nbytes]
+            raw = ring.dev[base + lf.offset: base + lf.offset + lf.nbytes]
             out.append(raw.view(lf.dtype).view(lf.shape))
-        return _unflatten(template, out), slot
+        return _unflatten(template, out), where
 
-    def release(self, slot) -> None:
-        if slot is None or self._handle is None:
+    def release(self, where) -> None:
+        if where is None:
+            return
+        ring, slot = where
+        if ring.handle is None:
             return
         stream = torch.cuda.current_stream(self.device).cuda_stream
-        N.check(self.lib.rk_stage_release(self._handle, slot, stream), "rk_stage_release")
+        N.check(self.lib.rk_stage_release(ring.handle, slot, stream), "rk_stage_release")
+        ring.outstanding -= 1
+        if ring.retired and ring.outstanding == 0:
+            ring.destroy()
+            self._old = [r for r in self._old if r is not ring]
 
     def close(self) -> None:
-        if self._handle is not None:
-            torch.cuda.synchronize(self.device)
-            self.lib.rk_stage_destroy(self._handle)
-            self._handle = None
-        self._pinned = self._dev = None
-        self.slot_bytes = 0
+        for ring in self._old + ([self._ring] if self._ring is not None else []):
+            ring.destroy()
+        self._old = []
+        self._ring = None
 
     def __del__(self):
         try:

@@ -137,11 +137,65 @@ def test_stager_roundtrip_and_ring_reuse():
                           (staged["z"][0], batch["z"][0]), (staged["z"][1], batch["z"][1])):
             assert got.device.type == "cuda" and got.dtype == want.dtype
             assert torch.equal(got.cpu(), want)
-        kept.append(slot)
+        kept.append(slot[1])
         st.release(slot)
     assert kept[:3] == [0, 1, 2] and kept[3] == 0
-    assert st.batches == 10
+    assert st.batches == 10 and st.rings_created == 2
     st.close()
+
+
+def test_stager_ring_grows_while_a_batch_is_pending():
+    """The loader submits batch k+1 before it collects batch k.  When k+1 does not fit the ring
+    (pad-to-longest batches), the ring is replaced by a larger one -- batch k must still come
+    out of the ring it was submitted to, with its own bytes.  (The first version rebuilt the
+    ring in place: batch k then read batch k+1's bytes, or an unknown ticket.)"""
+    from rocket_b200.staging import PinnedRingStager
+    dev = torch.device("cuda", torch.cuda.current_device())
+    st = PinnedRingStager(dev, slots=3, copy_threads=2)
+    g = torch.Generator().manual_seed(1)
+    sizes = [1000, 1200, 600_000, 1500, 2_000_000, 900, 800]     # two growths, pending each time
+    batches = [(torch.randn(n, 4, generator=g), torch.randint(0, 9, (n,), generator=g))
+               for n in sizes]
+    pending = st.submit(batches[0])
+    for k in range(len(batches)):
+        nxt = st.submit(batches[k + 1]) if k + 1 < len(batches) else None
+        staged, token = st.collect(pending)
+        assert torch.equal(staged[0].cpu(), batches[k][0]), k
+        assert torch.equal(staged[1].cpu(), batches[k][1]), k
+        st.release(token)
+        pending = nxt
+    assert st.rings_created == 3 and not st._old          # superseded rings were torn down
+    st.close()
+
+
+def test_loader_with_batches_that_grow_mid_epoch():
+    """The same through EngineDataLoader, the way the Dataset capsule drives it: a collate
+    function that pads to the longest sample makes later batches larger than the first."""
+    from rocket_b200.engine import Engine
+    lens = [8] * 8 + [8, 8, 8, 70_000] + [16] * 4 + [400_000, 3, 3, 3]
+
+    class Ragged(torch.utils.data.Dataset):
+        def __len__(self):
+            return len(lens)
+
+        def __getitem__(self, i):
+            return torch.full((lens[i],), float(i))
+
+    def pad(samples):
+        width = max(t.numel() for t in samples)
+        out = torch.zeros(len(samples), width)
+        for r, t in enumerate(samples):
+            out[r, :t.numel()] = t
+        return out
+
+    eng = Engine()
+    loader = eng.prepare(torch.utils.data.DataLoader(Ragged(), batch_size=4, collate_fn=pad))
+    seen = [b.cpu() for b in loader]
+    want = [pad([Ragged()[i] for i in range(k, k + 4)]) for k in range(0, len(lens), 4)]
+    assert len(seen) == len(want)
+    for k, (a, b) in enumerate(zip(seen, want)):
+        assert torch.equal(a, b), k
+    eng.end_training()
 
 
 def test_deferred_loss_does_not_sync_per_step():
@@ -196,7 +250,7 @@ def test_checkpoint_resume_is_bit_exact_and_torch_compatible(tmp_path):
     launcher, h1 = run(1, tag="a", save=True)
     launcher.launch()
     ckpt = tmp_path / "a" / "v0" / "weights" / "005"
-    sd = torch.load(ckpt / "optimizer_0.pt", map_location="cpu")
+    sd = torch.load(ckpt / "optimizer.bin", map_location="cpu")
     assert set(sd["state"][0]) >= {"step", "exp_avg", "exp_avg_sq"} and float(sd["state"][0]["step"]) == 6
     plain = torch.optim.AdamW(workloads.LeNet().parameters())
     plain.load_state_dict(sd)                                   # loads into stock torch
@@ -208,6 +262,18 @@ def test_checkpoint_resume_is_bit_exact_and_torch_compatible(tmp_path):
     launcher.resume(str(ckpt), load_capsules=False).launch()   # 6 restored + 6 new
     for (k, a), (_, b) in zip(h2["net"].named_parameters(), h3["net"].named_parameters()):
         assert torch.equal(a, b), k
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_resume_mid_epoch_with_capsule_state_on_gpu(tmp_path, graph):
+    """The reference's resume path on the CUDA engine (see the CPU twin in
+    tests/test_host_engine.py): checkpoint after batch 3 of a 6-batch epoch through a
+    Checkpointer capsule, resume with load_capsules=True in a fresh Launcher, finish: bitwise
+    the parameters, eval counts, loss values and step numbers of the uninterrupted run.  Also
+    with the step replayed from a CUDA graph (the restored run re-captures)."""
+    import rocket_b200 as rk
+    from test_host_engine import _resume_mid_epoch
+    _resume_mid_epoch(rk, tmp_path, **(dict(graph=True) if graph else {}))
 
 
 @pytest.mark.parametrize("name", ["adamw_accum2", "adamw_clip", "sgd_clip"])

@@ -7,7 +7,8 @@ slot, and cannot create a buffer of its own.  The entry point keeps its scratch 
 array inside the library (RK_STATIC_SCRATCH_BYTES per GPU) and allocates nothing.
 
 Checked here, through the C-ABI (ctypes), against the existing rk_l2norm_multi on the same
-plans: same total norm and per-tensor norms (the kernel is the same and deterministic, so the
+plans and against the CPU oracle (oracle.l2norm_multi, double accumulation) on the same
+gradients: same total norm and per-tensor norms (the kernel is the same and deterministic, so the
 bar is the 2 ulp the other norm tests use and the observed difference is zero), on calls made
 back to back -- including a small plan right after a large one, whose completion ticket then
 sits where the large plan left partial sums, so the entry point's own clearing is what makes
@@ -37,11 +38,15 @@ def _plan(sizes, seed):
     dev = torch.device("cuda", torch.cuda.current_device())
     be = NativeBackend(dev)
     g = torch.Generator().manual_seed(seed)
-    specs = []
+    specs, host = [], []
     for n in sizes:
-        grad = (torch.randn(n, generator=g) * 1e-2).to(dev)
+        grad = torch.randn(n, generator=g) * 1e-2
+        host.append(grad.numpy())
+        grad = grad.to(dev)
         specs.append(TensorSpec(p=grad.clone(), g=grad, m=None, v=None, group=0))
-    return be, be.make_plan(specs)
+    plan = be.make_plan(specs)
+    plan.host_grads = host            # for the oracle
+    return be, plan
 
 
 def _static_norm(plan, scale):
@@ -70,6 +75,12 @@ def _reference_norm(be, plan, scale):
     return tot.cpu().numpy().copy(), plan.tensor_norms.cpu().numpy().copy()
 
 
+def _oracle_norm(plan, scale):
+    import oracle
+    tot, per_tensor = oracle.l2norm_multi(plan.host_grads, scale)
+    return np.array([tot], np.float32), np.asarray(per_tensor, np.float32)
+
+
 def test_static_scratch_norm_matches_existing_entry_point_on_consecutive_calls():
     # large list first: ~25K norm chunks, its partial sums cover the low scratch offsets
     be_big, big = _plan([4096 * 6000 + 11, 4096 * 19000 + 3, 77], seed=1)
@@ -83,6 +94,9 @@ def test_static_scratch_norm_matches_existing_entry_point_on_consecutive_calls()
         assert np.isfinite(got_tot).all() and (got_tot > 0).all()
         assert _ulp(got_tot, want_tot) <= 2, (got_tot, want_tot)
         assert _ulp(got_tn, want_tn) <= 2
+        cpu_tot, cpu_tn = _oracle_norm(plan, scale)      # CUDA against the CPU restatement
+        assert _ulp(got_tot, cpu_tot) <= 2, (got_tot, cpu_tot)
+        assert _ulp(got_tn, cpu_tn) <= 2
 
 
 def test_static_scratch_norm_two_calls_in_a_row_same_plan():
@@ -90,8 +104,10 @@ def test_static_scratch_norm_two_calls_in_a_row_same_plan():
     want_tot, want_tn = _reference_norm(be, plan, 1.0)
     first = _static_norm(plan, 1.0)
     second = _static_norm(plan, 1.0)
+    cpu_tot, cpu_tn = _oracle_norm(plan, 1.0)
     for got_tot, got_tn in (first, second):
         assert _ulp(got_tot, want_tot) <= 2 and _ulp(got_tn, want_tn) <= 2
+        assert _ulp(got_tot, cpu_tot) <= 2 and _ulp(got_tn, cpu_tn) <= 2
 
 
 def test_static_scratch_norm_refuses_lists_beyond_its_limit():
