@@ -46,14 +46,28 @@ CASES = {
 #   "oracle"     optimizer arithmetic = oracle/step_oracle.c, i.e. torch's CPU kernels restated
 #                (the reference's step as pinned by the CPU suite).  The CUDA kernels spell the
 #                same rounding sequence, so parameters must agree BIT FOR BIT without clipping,
-#                and to the clip norm's last ulp with it.
+#                and to the clip norm's last ulp with it.  Bar: 1e-5 (north_star), 0 observed.
 #   "torch_cuda" optimizer arithmetic = torch.optim(foreach=False) CUDA kernels.  torch's CUDA
 #                elementwise kernels round differently from its own CPU kernels (division by a
 #                scalar becomes a multiply by the reciprocal, addcdiv/addcmul group the product
-#                differently); Adam's normalisation amplifies those ulps over steps.  Measured
-#                on B200: torch-CUDA vs torch-CPU-semantics = 1.1e-5 after 26 AdamW steps, and
-#                the engine sits exactly on the CPU side of that gap.  Bar here: 1e-4.
-ARMS = {"oracle": 1e-5, "torch_cuda": 1e-4}
+#                differently); Adam's normalisation amplifies those ulps over steps.  No
+#                constant is a meaningful bar for that: the distance is MEASURED in the test --
+#                the port with the oracle's arithmetic (= the reference's CPU semantics) is run
+#                too, and the engine must be no farther from torch-CUDA than that port is:
+#                    d(engine, torch_cuda) <= 1.1 * d(oracle_port, torch_cuda) + 1e-7.
+#                (On B200: both are 1.1e-5 after 26 AdamW steps; the engine equals the oracle
+#                port.)  A loose absolute cap keeps a wholesale divergence from hiding.
+ARMS = {"oracle": 1e-5, "torch_cuda": None}
+TORCH_CUDA_CAP = 1e-3
+
+
+def _total_rel(mine: dict, want: dict) -> float:
+    num = den = 0.0
+    for k, w in want.items():
+        g = mine[k].detach().cpu()
+        num += float((g - w).pow(2).sum())
+        den += float(w.pow(2).sum())
+    return (num / den) ** 0.5
 
 
 @pytest.mark.parametrize("name", list(CASES))
@@ -78,22 +92,29 @@ def test_capsule_graph_matches_port_on_gpu(name, clip_via, arm):
     lrs = [(s, d["opt.lr.0"]) for s, d in tracker.scalars if "opt.lr.0" in d]
     assert [s for s, _ in losses] == port["loss_steps"]
     assert [v for _, v in lrs] == port["lr_values"]
-    np.testing.assert_allclose([v for _, v in losses], port["loss_values"], rtol=1e-5)
+    np.testing.assert_allclose([v for _, v in losses], port["loss_values"],
+                               rtol=1e-5 if arm == "oracle" else 1e-4)
     # Meter counts: integers, bit-exact
     assert [tuple(x) for x in h["accuracy"].history] == \
         [tuple(x) for x in port["accuracy_history"]]
     # parameters after N optimizer steps, per tensor and overall
-    tol = ARMS[arm]
     mine = dict(h["net"].named_parameters())
-    num = den = 0.0
-    for k, want in port["params"].items():
-        got = mine[k].detach().cpu()
-        if arm == "oracle" and kw["max_norm"] is None:
-            assert torch.equal(got, want), f"{k}: not bit-exact against the oracle arm"
-        assert _rel(got, want) <= tol, (k, _rel(got, want))
-        num += float((got - want).pow(2).sum())
-        den += float(want.pow(2).sum())
-    assert (num / den) ** 0.5 <= tol
+    if arm == "oracle":
+        tol = ARMS[arm]
+        for k, want in port["params"].items():
+            got = mine[k].detach().cpu()
+            if kw["max_norm"] is None:
+                assert torch.equal(got, want), f"{k}: not bit-exact against the oracle arm"
+            assert _rel(got, want) <= tol, (k, _rel(got, want))
+        assert _total_rel(mine, port["params"]) <= tol
+    else:
+        # the reference's CPU semantics on the same GPU forward/backward, for the triangle
+        ref = looper_port.run_mnist_port(device="cuda", workloads=workloads,
+                                         optimizer_impl="oracle", **kw)
+        d_engine = _total_rel(mine, port["params"])
+        d_reference = _total_rel({k: v for k, v in ref["params"].items()}, port["params"])
+        assert d_engine <= 1.1 * d_reference + 1e-7, (d_engine, d_reference)
+        assert d_engine <= TORCH_CUDA_CAP, d_engine
     if arm == "oracle":
         # the loss the engine accumulated on the device equals the host-side doubles
         assert [v for _, v in losses] == port["loss_values"]
@@ -349,22 +370,36 @@ def test_fp16_loss_scaling_matches_gradscaler_port_on_gpu(name, arm):
     assert [s for s, _ in losses] == port["loss_steps"]
     # (torch_cuda arm: torch's CUDA AdamW rounds differently from its CPU kernels -- see ARMS --
     # and the fp16 forward amplifies that into the loss after a few steps: measured 2.1e-5)
-    np.testing.assert_allclose([v for _, v in losses], port["loss_values"], rtol=ARMS[arm])
-    if arm == "oracle" and kw["max_norm"] is None:
-        assert [v for _, v in losses] == port["loss_values"]
-    counts = np.array(h["accuracy"].history) - np.array(port["accuracy_history"])
-    if arm == "oracle":
-        assert not counts.any()                       # Meter counts: bit-exact
-    else:
-        # the same arithmetic gap can flip a near-tied fp16 argmax in eval (measured: 1 of 333)
-        assert np.abs(counts).max() <= 2
-    tol = ARMS[arm] if arm == "oracle" else 1e-3      # sanity arm under fp16; "oracle" is the bar
     mine = dict(h["net"].named_parameters())
-    for k, want in port["params"].items():
-        got = mine[k].detach().cpu()
-        if arm == "oracle" and kw["max_norm"] is None:
-            assert torch.equal(got, want), f"{k}: not bit-exact against the oracle arm"
-        assert _rel(got, want) <= tol, (k, _rel(got, want))
+    if arm == "oracle":
+        np.testing.assert_allclose([v for _, v in losses], port["loss_values"], rtol=ARMS[arm])
+        if kw["max_norm"] is None:
+            assert [v for _, v in losses] == port["loss_values"]
+        counts = np.array(h["accuracy"].history) - np.array(port["accuracy_history"])
+        assert not counts.any()                       # Meter counts: bit-exact
+        for k, want in port["params"].items():
+            got = mine[k].detach().cpu()
+            if kw["max_norm"] is None:
+                assert torch.equal(got, want), f"{k}: not bit-exact against the oracle arm"
+            assert _rel(got, want) <= ARMS[arm], (k, _rel(got, want))
+        return
+    # torch_cuda arm, measured (see ARMS): the reference's CPU semantics under GradScaler on the
+    # same GPU is the yardstick; the engine must be no farther from torch-CUDA than it is, in
+    # parameters, in the loss series and in eval counts (a near-tied fp16 argmax can flip).
+    ref = looper_port.run_mnist_port(device="cuda", workloads=workloads, optimizer_impl="oracle",
+                                     **kw)
+    d_engine = _total_rel(mine, port["params"])
+    d_reference = _total_rel(ref["params"], port["params"])
+    assert d_engine <= 1.1 * d_reference + 1e-7, (d_engine, d_reference)
+    assert d_engine <= TORCH_CUDA_CAP, d_engine
+    want_l = np.array(port["loss_values"])
+    l_engine = np.abs(np.array([v for _, v in losses]) - want_l).max()
+    l_reference = np.abs(np.array(ref["loss_values"]) - want_l).max()
+    assert l_engine <= 1.1 * l_reference + 1e-9, (l_engine, l_reference)
+    c_engine = np.abs(np.array(h["accuracy"].history) - np.array(port["accuracy_history"])).max()
+    c_reference = np.abs(np.array(ref["accuracy_history"])
+                         - np.array(port["accuracy_history"])).max()
+    assert c_engine <= c_reference, (c_engine, c_reference)
 
 
 def test_fp16_overflow_skips_the_step_and_backs_the_scale_off():

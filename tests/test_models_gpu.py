@@ -156,3 +156,29 @@ def test_config4_gpt2_accum4_adamw_clip_bf16(arm):
     mine = _engine_run(net_b, NextToken(), torch.optim.AdamW(net_b.parameters(), **hp), batches,
                        accum=4, max_norm=1.0, mixed_precision="bf16")
     _compare(mine, port["params"], ARMS[arm])
+
+
+def test_config4_full_size_gpt2_two_accumulation_cycles_oracle_arm():
+    """The real configs[3] model -- GPT2LMHeadModel(GPT2Config()): 124,439,808 parameters in 148
+    tensors, lm_head tied to wte, 98 tensors under 4096 elements -- through two accumulation
+    cycles (8 micro-batches, 2 optimizer steps) of the capsule graph, against the looper port
+    with the C oracle's arithmetic on the same GPU forward/backward.  Sequences are short (the
+    arithmetic under test is the accumulate / no-sync / clip / fused-step path over the real
+    tensor list, not the attention cost)."""
+    from transformers import GPT2Config, GPT2LMHeadModel
+    torch.manual_seed(0)
+    base = GPTBatch(GPT2LMHeadModel(GPT2Config(resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)))
+    params = dict(base.named_parameters())
+    assert len(params) == 148 and sum(p.numel() for p in params.values()) == 124_439_808
+    assert base.lm.lm_head.weight is base.lm.transformer.wte.weight
+    g = torch.Generator().manual_seed(4)
+    batches = [[torch.randint(0, 50257, (2, 128), generator=g)] for _ in range(8)]
+    hp = dict(lr=6e-4, betas=(0.9, 0.95), weight_decay=0.1, foreach=False)
+    net_a, net_b = copy.deepcopy(base), copy.deepcopy(base)
+    port = looper_port.run_generic_port(
+        net_a, NextToken(), torch.optim.AdamW(net_a.parameters(), **hp), batches, accum=4,
+        max_norm=1.0, device="cuda", autocast_dtype=torch.bfloat16, optimizer_impl="oracle")
+    mine = _engine_run(net_b, NextToken(), torch.optim.AdamW(net_b.parameters(), **hp), batches,
+                       accum=4, max_norm=1.0, mixed_precision="bf16")
+    _compare(mine, port["params"], 1e-5)
+    assert net_b.lm.lm_head.weight.data_ptr() == net_b.lm.transformer.wte.weight.data_ptr()

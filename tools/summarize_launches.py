@@ -27,7 +27,7 @@ def main() -> None:
         except ValueError:
             continue
         rows.append((r["Kernel Name"], ns))
-    marks = [i for i, (k, _) in enumerate(rows) if "rk_step_kernel" in k]
+    marks = [i for i, (k, _) in enumerate(rows) if "rk_step_kernel" in k or "rk_step_bulk_kernel" in k]
     spans = [(a + 1, b + 1) for a, b in zip(marks, marks[1:])]       # (after step i, through step i+1]
     sizes = [b - a for a, b in spans]
     # steady state: the last run of n_steps spans with the same number of launches
