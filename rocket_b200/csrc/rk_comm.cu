@@ -19,6 +19,8 @@
 // all peers have mapped (CUDA IPC, done by the host side); peers.arena[q] is rank q's arena
 // as seen from this rank.  Cross-GPU flags carry a monotonically increasing epoch, so they
 // never need resetting.
+#include <stdlib.h>
+
 #include "rk_common.cuh"
 #include "rk_step_ops.cuh"
 
@@ -86,7 +88,7 @@ __device__ __forceinline__ void mc_st1(float* mc, float v) {
 // MC = true : multimem.ld_reduce / multimem.st on the arenas' multicast mapping -- the switch
 //             does the W-way sum and the W-way replication, so each GPU sends and receives
 //             about G bytes instead of 2(W-1)/W * G (worth it from W = 4 up).
-template <int W, bool MC>
+template <int W, bool MC, int UMC>
 __global__ void __launch_bounds__(COMM_THREADS)
 rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
                          const char* __restrict__ plan, unsigned long long scratch_off,
@@ -134,15 +136,15 @@ rk_allreduce_norm_kernel(const CommPeers peers, char* mc_arena, int rank,
         float* m = reinterpret_cast<float*>(mc_arena + off);
         if ((off & 15) == 0) {
           const int nvec = count >> 2;
-          for (int i0 = tid; i0 < nvec; i0 += COMM_THREADS * COMM_UNROLL_MC) {
-            float4 s[COMM_UNROLL_MC];
+          for (int i0 = tid; i0 < nvec; i0 += COMM_THREADS * UMC) {
+            float4 s[UMC];
 #pragma unroll
-            for (int k = 0; k < COMM_UNROLL_MC; ++k) {
+            for (int k = 0; k < UMC; ++k) {
               const int i = i0 + k * COMM_THREADS;
               if (i < nvec) s[k] = mc_ld_reduce4(m + 4 * i);
             }
 #pragma unroll
-            for (int k = 0; k < COMM_UNROLL_MC; ++k) {
+            for (int k = 0; k < UMC; ++k) {
               const int i = i0 + k * COMM_THREADS;
               if (i < nvec) {
                 s[k].x = __fmul_rn(s[k].x, scale); s[k].y = __fmul_rn(s[k].y, scale);
@@ -327,15 +329,27 @@ static int launch_exchange(rk_comm* c, const void* plan_host, const void* plan_d
   const float scale = 1.0f / (float)W;
   cudaStream_t s = (cudaStream_t)stream;
   const bool mc = c->mc_arena != nullptr && use_multicast != 0;
-#define RK_LAUNCH(WW, MC)                                                                    \
-  rk_allreduce_norm_kernel<WW, MC><<<grid, COMM_THREADS, 0, s>>>(c->peers, c->mc_arena,      \
+  // multimem loads a thread keeps in flight (tuning: RK_COMM_MC_UNROLL = 2 | 4 | 8)
+  int umc = COMM_UNROLL_MC;
+  if (mc) {
+    const char* e = getenv("RK_COMM_MC_UNROLL");
+    if (e) umc = atoi(e);
+  }
+#define RK_LAUNCH(WW, MC, U)                                                                 \
+  rk_allreduce_norm_kernel<WW, MC, U><<<grid, COMM_THREADS, 0, s>>>(c->peers, c->mc_arena,   \
       c->rank, (const char*)plan_dev, c->scratch_off, chunk_lo, chunk_hi, bucket, scale,    \
       broadcast)
+#define RK_LAUNCH_W(WW)                                                                      \
+  if (!mc) RK_LAUNCH(WW, false, 4);                                                          \
+  else if (umc == 2) RK_LAUNCH(WW, true, 2);                                                 \
+  else if (umc == 8) RK_LAUNCH(WW, true, 8);                                                 \
+  else RK_LAUNCH(WW, true, 4)
   switch (W) {
-    case 2: if (mc) RK_LAUNCH(2, true); else RK_LAUNCH(2, false); break;
-    case 4: if (mc) RK_LAUNCH(4, true); else RK_LAUNCH(4, false); break;
-    case 8: if (mc) RK_LAUNCH(8, true); else RK_LAUNCH(8, false); break;
+    case 2: RK_LAUNCH_W(2); break;
+    case 4: RK_LAUNCH_W(4); break;
+    case 8: RK_LAUNCH_W(8); break;
   }
+#undef RK_LAUNCH_W
 #undef RK_LAUNCH
   RK_CUDA(cudaGetLastError());
   g_rk_launches.fetch_add(1);
