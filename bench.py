@@ -472,9 +472,10 @@ def exchange_summary(res, world: int):
         per_step_ms = statistics.mean(res["exchange_graph_ms"])
         per_step_bytes = res["exchange_graph_bytes"]
         launches = None
-        how = ("external CUDA events inside the replayed graph, first bucket launch to last "
-               "bucket end; read for the last replay of the timed region and 8 synchronised "
-               "replays after it")
+        how = ("external CUDA event pairs around every bucket's kernel inside the replayed graph "
+               "(launched from the gradient hooks during capture: they run beside the rest of "
+               "backward), summed; read for the last replay of the timed region and 8 "
+               "synchronised replays after it")
     else:
         return None
     bus = 2 * (world - 1) / world * per_step_bytes / (per_step_ms * 1e-3) / 1e9

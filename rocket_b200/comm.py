@@ -162,7 +162,7 @@ class P2PGradSync(_BucketedSync):
         self.timings: list = []     # (bucket bytes, start event, end event) on self.stream
         # graph-captured steps: one external event pair around all buckets of the step, as
         # event-record nodes of the graph (re-recorded by every replay); bench.py samples it
-        self.graph_ev = None
+        self.graph_ev: list = []    # (bucket bytes, start, end) per bucket
         self.graph_ms: list = []
         self.graph_bytes = 0
         ptrs, self.multicast_ptr, self._peers = map_arena(opt.arena, engine)
@@ -182,9 +182,16 @@ class P2PGradSync(_BucketedSync):
         dist.barrier()         # every rank has mapped every arena (and they are zero-filled)
 
     def _can_launch(self) -> bool:
-        # While a CUDA graph of the step is being captured the buckets are issued from
-        # finish(), on the capturing thread, instead of from autograd's hook thread.
-        return self.opt._plan is not None and self.engine.graph_pass is None
+        # Also while a CUDA graph of the step is being captured: stream capture follows streams,
+        # not threads, so a bucket launched from autograd's hook thread onto the side stream --
+        # forked from the capturing stream by the event in _launch, joined back in finish() --
+        # becomes a node that runs beside the rest of backward in every replay.  (On replays no
+        # hook fires: backward is inside the graph.)  ROCKET_B200_GRAPH_OVERLAP=0 issues the
+        # buckets from finish() instead, after backward.
+        gp = self.engine.graph_pass
+        if gp is not None and (gp.mode != "capture" or not self.graph_overlap):
+            return False
+        return self.opt._plan is not None
 
     def _chunk_range(self, b: int) -> tuple[int, int]:
         first, last = self.param_ranges[b]
@@ -198,54 +205,53 @@ class P2PGradSync(_BucketedSync):
         self._event.record(torch.cuda.current_stream(self.engine.device))
         self.stream.wait_event(self._event)
         e0, e1 = self.buckets[b]
-        if self.profile:
-            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        gp = self.engine.graph_pass
+        capturing = gp is not None and gp.mode == "capture"
+        timed = self.graph_timing if capturing else self.profile
+        if capturing and not any(self._launched):
+            self.graph_ev = []           # first bucket of the step being captured
+        if timed:
+            # inside a capture: external events = event-record nodes, re-recorded by every replay
+            kw = dict(enable_timing=True, external=True) if capturing else dict(enable_timing=True)
+            t0, t1 = torch.cuda.Event(**kw), torch.cuda.Event(**kw)
             t0.record(self.stream)
         exchange = self.backend.comm_allreduce_norm if self.broadcast \
             else self.backend.comm_reduce_scatter_norm
         exchange(self._comm, plan, lo, hi, b, self.max_ctas, self.stream.cuda_stream,
                  self.use_multicast)
-        if self.profile:
+        if timed:
             t1.record(self.stream)
-            self.timings.append(((e1 - e0) * 4, t0, t1))
+            if capturing:
+                self.graph_ev.append(((e1 - e0) * 4, t0, t1))
+            else:
+                self.timings.append(((e1 - e0) * 4, t0, t1))
         self._launched[b] = True
         self.bytes_reduced += (e1 - e0) * 4
 
     def _wait(self) -> None:
         torch.cuda.current_stream(self.engine.device).wait_stream(self.stream)
 
-    def finish(self) -> bool:
-        gp = self.engine.graph_pass
-        if gp is None or gp.mode != "capture" or not self.graph_timing or self._finished:
-            return super().finish()
-        # being captured: every bucket is issued from here; bracket them on the side stream
-        t0 = torch.cuda.Event(enable_timing=True, external=True)
-        t1 = torch.cuda.Event(enable_timing=True, external=True)
-        self._event.record(torch.cuda.current_stream(self.engine.device))
-        self.stream.wait_event(self._event)
-        t0.record(self.stream)
-        before = self.bytes_reduced
-        for b in range(len(self.buckets)):
-            if not self._launched[b]:
-                self._launch(b)
-        t1.record(self.stream)
-        self.graph_ev, self.graph_bytes = (t0, t1), self.bytes_reduced - before
-        self._wait()
-        self._finished = True
-        return self.fused_norm
-
-    #: bench.py sets this to put the event pair above into captured steps
+    #: bench.py sets this to bracket every bucket's kernel inside captured steps with events
     graph_timing = False
+    #: launch buckets from the gradient hooks during capture (overlap with backward in replays)
+    graph_overlap = os.environ.get("ROCKET_B200_GRAPH_OVERLAP", "1") == "1"
 
     def sample_graph_events(self) -> None:
-        if self.graph_ev is None:
+        """One sample of the exchange's kernel time per step from the in-graph event pairs (sum
+        over the buckets), if the last replay has completed and the pairs are consistent."""
+        if not self.graph_ev:
             return
         try:
-            s, e = self.graph_ev
-            if e.query():
+            total = 0.0
+            for _, s, e in self.graph_ev:
+                if not e.query():
+                    return
                 dt = s.elapsed_time(e)
-                if 0.0 < dt < 50.0:              # a torn pair (replay in flight) is negative
-                    self.graph_ms.append(dt)
+                if not 0.0 < dt < 50.0:          # a torn pair (replay in flight) is negative
+                    return
+                total += dt
+            self.graph_ms.append(total)
+            self.graph_bytes = sum(nb for nb, _, _ in self.graph_ev)
         except Exception:
             pass
 
@@ -330,34 +336,32 @@ def broadcast_module_state(module: torch.nn.Module, src: int = 0) -> None:
 
 class BufferSync:
     """DDP's ``broadcast_buffers=True``: rank 0's module buffers (BatchNorm statistics)
-    overwrite everyone's before a training forward.  Buffers are re-homed into one flat
-    tensor per dtype so this is one collective per dtype, without packing copies."""
+    overwrite everyone's before a training forward.  All buffers, whatever their dtype, are
+    re-homed into ONE flat byte buffer (16-byte aligned segments), so this is a single small
+    collective per forward without packing copies (it was one per dtype: float statistics and
+    the int64 batch counters)."""
 
     def __init__(self, module: torch.nn.Module):
-        self.flats: list[torch.Tensor] = []
-        by_dtype: dict = {}
-        for b in module.buffers():
-            by_dtype.setdefault(b.dtype, []).append(b)
-        with torch.no_grad():
-            for dtype, bufs in by_dtype.items():
-                total = sum(b.numel() for b in bufs)
-                if total == 0:
-                    continue
-                flat = torch.empty(total, dtype=dtype, device=bufs[0].device)
-                off = 0
-                for b in bufs:
-                    n = b.numel()
-                    view = flat[off:off + n].view(b.shape)
+        bufs = [b for b in module.buffers() if b.numel() > 0]
+        self.flat = None
+        if bufs:
+            offs, total = [], 0
+            for b in bufs:
+                offs.append(total)
+                total += -(-(b.numel() * b.element_size()) // 16) * 16
+            self.flat = torch.zeros(total, dtype=torch.uint8, device=bufs[0].device)
+            with torch.no_grad():
+                for b, off in zip(bufs, offs):
+                    nbytes = b.numel() * b.element_size()
+                    view = self.flat[off:off + nbytes].view(b.dtype).view(b.shape)
                     view.copy_(b)
                     b.data = view
-                    off += n
-                self.flats.append(flat)
+        self.flats = [self.flat] if self.flat is not None else []
         self._handle = module.register_forward_pre_hook(self._hook)
 
     def _hook(self, module, args):
-        if torch.is_grad_enabled() and module.training:
-            for flat in self.flats:
-                dist.broadcast(flat, src=0)
+        if self.flat is not None and torch.is_grad_enabled() and module.training:
+            dist.broadcast(self.flat, src=0)
         return None
 
     def remove(self) -> None:
