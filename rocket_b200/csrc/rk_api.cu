@@ -60,10 +60,11 @@ int rk_persistent_grid(const void* kernel, int block, size_t dyn_smem, int n_wor
 
 // ---- plan ---------------------------------------------------------------------
 static int norm_chunk_for(int64_t total) {
-  // Aim for <= ~32K norm chunks so the in-kernel final reduction stays short, but
+  // Aim for <= ~16K norm chunks: level 1 runs one block-wide reduction per chunk, so a chunk
+  // should be at least two load batches (8192 elements) once the list is large, but
   // keep chunks small enough that 148 SMs x resident CTAs balance.
   int64_t c = RK_NORM_CHUNK_MIN;
-  while (total / c > 32768 && c < (1 << 20)) c <<= 1;
+  while (total / c > 16384 && c < (1 << 20)) c <<= 1;
   return (int)c;
 }
 
