@@ -83,3 +83,41 @@ def test_sharded_batch_sampler_even_batches():
         assert all(len(b) == bs for s in out for b in s)       # all full sized
         seen = [i for step in zip(*out) for b in step for i in b]
         assert seen[:n] == list(range(n))                      # gather order = dataset order
+
+
+def test_sharded_batch_sampler_known_cases_from_accelerate():
+    """Expected shards written out by hand, the cases accelerate's own
+    tests/test_data_loader.py::test_batch_sampler_shards_with_no_splits checks (recalled, the
+    package is not on the image): batch size 3, two processes, even_batches.  Both the engine's
+    sampler and the test shim's restatement (which the goldens were generated through) must
+    give them -- the one place where accelerate-level semantics are pinned by something other
+    than this repository's own restatement."""
+    import sys
+    from torch.utils.data import BatchSampler
+    import oracle
+    from rocket_b200.staging import ShardedBatchSampler
+    if str(oracle.SHIMS) not in sys.path:
+        sys.path.insert(0, str(oracle.SHIMS))
+    from accelerate import BatchSamplerShard          # the shim's class
+
+    cases = {
+        24: ([[0, 1, 2], [6, 7, 8], [12, 13, 14], [18, 19, 20]],
+             [[3, 4, 5], [9, 10, 11], [15, 16, 17], [21, 22, 23]]),
+        21: ([[0, 1, 2], [6, 7, 8], [12, 13, 14], [18, 19, 20]],          # odd number of batches
+             [[3, 4, 5], [9, 10, 11], [15, 16, 17], [0, 1, 2]]),
+        22: ([[0, 1, 2], [6, 7, 8], [12, 13, 14], [18, 19, 20]],          # short batch on rank 1
+             [[3, 4, 5], [9, 10, 11], [15, 16, 17], [21, 0, 1]]),
+        20: ([[0, 1, 2], [6, 7, 8], [12, 13, 14], [18, 19, 0]],           # short batch on rank 0
+             [[3, 4, 5], [9, 10, 11], [15, 16, 17], [1, 2, 3]]),
+        2: ([[0, 1, 0]], [[1, 0, 1]]),                                    # smaller than one batch
+    }
+    for n, want in cases.items():
+        base = BatchSampler(range(n), batch_size=3, drop_last=False)
+        for cls in (ShardedBatchSampler, BatchSamplerShard):
+            got = tuple(list(cls(base, 2, r)) for r in range(2))
+            assert got == want, (n, cls.__name__, got)
+    # drop_last: incomplete rounds and short batches are dropped
+    base = BatchSampler(range(22), batch_size=3, drop_last=True)         # 7 full batches
+    for cls in (ShardedBatchSampler, BatchSamplerShard):
+        got = [list(cls(base, 2, r)) for r in range(2)]
+        assert got == [[[0, 1, 2], [6, 7, 8], [12, 13, 14]], [[3, 4, 5], [9, 10, 11], [15, 16, 17]]]
