@@ -77,11 +77,11 @@ class Module(Dispatcher):
             return False
         if getattr(engine, "scaler", None) is not None:
             return False     # fp16: the overflow decision is a host read between norm and step
-        # multi-GPU: only the hand-written NVLink exchange is replayable (device-side epochs);
-        # with a sharded optimizer step the step stays eager
+        # multi-GPU: only the hand-written NVLink exchange is replayable (device-side epochs),
+        # with the replicated or the sharded optimizer step
         return engine.num_processes == 1 or (
             bool(engine.grad_sync_kinds)
-            and all(k == "P2PGradSync" for k in engine.grad_sync_kinds))
+            and all(k.startswith("P2PGradSync") for k in engine.grad_sync_kinds))
 
     def _launch_graphed(self, attrs: Attributes) -> None:
         from rocket_b200.engine import GraphPass

@@ -335,17 +335,24 @@ class EngineOptimizer:
                 norm = None
         groups = self._step_groups()
         if self.sharded:
-            if gp is not None:
-                raise NotImplementedError("Module(graph=True) with a sharded optimizer step")
+            # the sharded kernel always reads its constants from the device table; inside a
+            # graph pass the upload moves in front of the replay (gp.pre), as for the replicated
+            # step, and the launch itself is captured once (its barrier epoch lives on the device)
             slot, uploaded = self._table_slot()
             eng.backend.step_table_write(self._kind, groups, slot)
-            self._dev_table.copy_(slot, non_blocking=True)
-            uploaded.record()
-            sync = eng.grad_sync_of(self)
-            eng.backend.comm_sharded_step(
-                sync._comm, plan, self._kind, self._dev_table.data_ptr(), norm,
-                float(max_norm) if max_norm is not None else 0.0, sync.step_ctas,
-                sync.use_multicast, self.shard_m, self.shard_v)
+            table = self._dev_table
+            if gp is None:
+                table.copy_(slot, non_blocking=True)
+                uploaded.record()
+            else:
+                gp.post.append(uploaded.record)
+                gp.pre.append(lambda: table.copy_(slot, non_blocking=True))
+            if not replay:
+                sync = eng.grad_sync_of(self)
+                eng.backend.comm_sharded_step(
+                    sync._comm, plan, self._kind, table.data_ptr(), norm,
+                    float(max_norm) if max_norm is not None else 0.0, sync.step_ctas,
+                    sync.use_multicast, self.shard_m, self.shard_v)
         elif gp is None:
             fn = eng.backend.sgd_step if self._kind == "sgd" else eng.backend.adam_step
             fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)

@@ -124,6 +124,28 @@ def test_graph_captured_step_with_nvlink_exchange_equals_eager(tmp_path):
     assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
 
 
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("case", ["ws2_adamw_clip", "ws2_sgd"])
+def test_graph_captured_sharded_step_equals_eager_replicated(case, tmp_path):
+    """Module(graph=True) together with Optimizer(sharded=True): reduce-scatter, the sharded
+    step kernel (constants from the device table, barrier epoch on the device) and the
+    parameter push are nodes of the replayed graph; the run must equal the eager replicated
+    two-GPU run bit for bit on both ranks."""
+    mp.spawn(_gpu_worker, args=(2, 29866, case, str(tmp_path), "p2p", False, False), nprocs=2,
+             join=True)
+    mp.spawn(_gpu_worker, args=(2, 29867, case, str(tmp_path), "p2p", True, True), nprocs=2,
+             join=True)
+    a = np.load(tmp_path / f"{case}_p2p_rank0.npz")
+    for r in range(2):
+        b = np.load(tmp_path / f"{case}_p2p_sharded_rank{r}.npz")
+        for k in a.files:
+            if k.startswith(("param/", "state/")):
+                assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), (r, k)
+        assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
+    b0 = np.load(tmp_path / f"{case}_p2p_sharded_rank0.npz")
+    assert a["loss_values"].tolist() == b0["loss_values"].tolist()
+
+
 @pytest.mark.parametrize("world", [2, 4])
 @pytest.mark.parametrize("case", list(dist_worker.WS2_CASES))
 def test_sharded_optimizer_step_equals_replicated_bitwise(case, world, tmp_path):
