@@ -517,7 +517,7 @@ def capsule_object(wl, res, res_e2e, peak):
     return out
 
 
-def torch_gpu_baseline(wl, steps: int, warmup: int):
+def torch_gpu_baseline(wl, steps: int, warmup: int, tf32_conv: bool = False):
     """Baseline B: the same step with stock torch on the same GPU(s)
     and no capsules -- torch.optim.AdamW(fused=True) + clip_grad_norm_(foreach=True) +
     zero_grad(set_to_none=True), DistributedDataParallel at N > 1.  That is the strongest path
@@ -526,7 +526,7 @@ def torch_gpu_baseline(wl, steps: int, warmup: int):
     import workloads
     rank, world, local = env_ranks()
     dev = torch.device("cuda", local)
-    set_precision(wl)
+    set_precision(wl, tf32_conv)
     net = wl["net"]().to(dev)
     model = net
     if world > 1:
@@ -702,6 +702,14 @@ def run_ours(args) -> dict:
             "e2e": {"value": round(tfe["value"], 1), "ms_per_step": round(tfe["ms_per_step"], 4)},
             "step_kernel_ms": round(k2t, 5),
             "step_kernel_gbs": round(algo * tf["n_params"] / (k2t * 1e-3) / 1e9, 1)}
+        # the same two comparisons at this precision: unchanged script, and stock torch
+        tfe_eager = run_capsule(wl, graph=False, steps=min(K, 50), warmup=max(5, args.warmup // 2),
+                                e2e=False, tf32_conv=True)
+        out["tf32_conv"]["eager"] = {"value": round(tfe_eager["value"], 1),
+                                     "ms_per_step": round(tfe_eager["ms_per_step"], 4)}
+        tft = torch_gpu_baseline(wl, steps=min(K, 50), warmup=max(5, args.warmup // 2),
+                                 tf32_conv=True)
+        out["tf32_conv"]["torch_gpu"] = {"value": tft["value"], "ms_per_step": tft["ms_per_step"]}
         # configs[2]: the workload the north_star puts the >= 7x scaling target on
         w50 = WORKLOADS["resnet50"]
         r50 = run_capsule(w50, graph=False, steps=args.r50_steps, warmup=5, e2e=False)

@@ -120,6 +120,29 @@ def test_capsule_graph_matches_port_on_gpu(name, clip_via, arm):
         assert [v for _, v in losses] == port["loss_values"]
 
 
+def test_capsule_graph_matches_port_with_tf32_convolutions():
+    """torch's default precision on Ampere and later: cuDNN convolutions in TF32 (what
+    bench.py reports as `tf32_conv`).  Forward and backward are shared by both arms, so the
+    engine must still equal the port with the oracle's arithmetic: same loss series, same
+    counts, parameters to the clip norm's last ulp."""
+    import rocket_b200 as rk
+    from rocket_b200.metrics import Accuracy
+    from rocket_b200.tracking import MemoryTracker
+    torch.backends.cudnn.allow_tf32 = True
+    kw = CASES["adamw_clip"]
+    port = looper_port.run_mnist_port(device="cuda", workloads=workloads,
+                                      optimizer_impl="oracle", **kw)
+    tracker = MemoryTracker("memory")
+    launcher, h = workloads.build_mnist_graph(rk, tracker_backend=tracker, clip_via="kwarg",
+                                              accuracy_cls=Accuracy, **kw)
+    launcher.launch()
+    losses = [d["train_loss"] for _, d in tracker.scalars if "train_loss" in d]
+    assert losses == port["loss_values"]
+    assert [tuple(x) for x in h["accuracy"].history] == \
+        [tuple(x) for x in port["accuracy_history"]]
+    assert _total_rel(dict(h["net"].named_parameters()), port["params"]) <= 1e-5
+
+
 def test_user_metric_through_gather_path_matches_device_metric():
     """A user-written Metric (the example's, corrected) still works: Meter gathers for it."""
     import rocket_b200 as rk
