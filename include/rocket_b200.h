@@ -110,7 +110,8 @@ int rk_plan_build(const rk_tensor_desc* descs, int n_tensors, void* plan_host,
  * two-level form of torch.nn.utils.clip_grad_norm_ / _get_total_norm
  * ($TORCH/nn/utils/clip_grad.py:96-107), which accelerate's clip_grad_norm_ calls.
  * Deterministic: per-chunk partials in a fixed order, no float atomics, so every
- * data-parallel rank derives a bit-identical clip coefficient.
+ * data-parallel rank derives a bit-identical clip coefficient.  Two launches on `stream`:
+ * level 1 (partials) and the one-CTA level 2 of rk_l2norm_finalize.
  * Writes total to *total_norm_dev (device float) and, if non-null, per-tensor norms
  * to tensor_norms_dev[n_tensors].  Tensors flagged RK_TENSOR_SKIP contribute 0.   */
 int rk_l2norm_multi(const void* plan_host, const void* plan_dev, float grad_scale,
@@ -150,7 +151,10 @@ int rk_l2norm_multi_static(const void* plan_host, const void* plan_dev, float gr
                            float* total_norm_dev, float* tensor_norms_dev, void* stream);
 
 /* Level 2 of K1 on its own: per-tensor norms and the total from per-chunk partials that are
- * already in scratch (rk_comm_allreduce_norm writes them).  Same fixed-order reduction.   */
+ * already in scratch (rk_comm_allreduce_norm writes them).  Same fixed-order reduction: it is
+ * the very kernel rk_l2norm_multi launches behind its level-1 kernel (one CTA, launched as a
+ * programmatic dependent so that its set-up overlaps the producer's tail), hence the same
+ * bits whichever kernel produced the partials.                                            */
 int rk_l2norm_finalize(const void* plan_host, const void* plan_dev, void* scratch_dev,
                        float* total_norm_dev, float* tensor_norms_dev, void* stream);
 
