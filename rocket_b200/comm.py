@@ -47,15 +47,30 @@ class _BucketedSync:
         self.bucket_of: list[int] = [0] * len(opt._params)
         self._members: list[list[int]] = []
         cap = int(first_bucket_mb * (1 << 20)) // 4
-        big = int(bucket_cap_mb * (1 << 20)) // 4
+        big = int(float(os.environ.get("ROCKET_B200_BUCKET_MB", bucket_cap_mb)) * (1 << 20)) // 4
+        # the bucket that holds parameter 0 completes last, when backward is over: whatever it
+        # carries is exchanged with nothing left to hide behind, so it is kept small
+        tail = int(float(os.environ.get("ROCKET_B200_TAIL_BUCKET_MB", 1.0)) * (1 << 20)) // 4
+        sizes = [p.numel() for p in opt._params]
+        tail_first = 0                      # parameters [0, tail_first] form the tail bucket
+        acc = 0
+        for i, n in enumerate(sizes):
+            acc += n
+            tail_first = i
+            if acc >= tail:
+                break
         hi = opt._total
         members: list[int] = []
         size = 0
         # walk parameters backwards: gradients become ready roughly in reverse order
         for i in range(len(opt._params) - 1, -1, -1):
             members.append(i)
-            size += opt._params[i].numel()
-            if size >= cap or i == 0:
+            size += sizes[i]
+            at_tail = i == tail_first + 1 and tail > 0
+            # elements still to come before the tail bucket: do not leave a sliver behind
+            left = sum(sizes[tail_first + 1:i]) if i > tail_first + 1 else 0
+            close = i == 0 or at_tail or (size >= cap and (left >= big // 8 or i <= tail_first))
+            if close:
                 lo = opt._offsets[i]
                 b = len(self.buckets)
                 self.buckets.append((lo, hi))
@@ -123,7 +138,7 @@ class _BucketedSync:
 class GradSync(_BucketedSync):
     """NCCL (or gloo) in-place SUM all-reduce per bucket."""
 
-    def __init__(self, opt, engine, bucket_cap_mb: float = 32.0):
+    def __init__(self, opt, engine, bucket_cap_mb: float = 16.0):
         super().__init__(opt, engine, bucket_cap_mb)
         self._works: list = []
         self.grad_scale = 1.0 / engine.num_processes
@@ -147,7 +162,7 @@ class P2PGradSync(_BucketedSync):
     fused_norm = True
     grad_scale = 1.0           # the kernel already wrote averaged gradients
 
-    def __init__(self, opt, engine, bucket_cap_mb: float = 32.0):
+    def __init__(self, opt, engine, bucket_cap_mb: float = 16.0):
         super().__init__(opt, engine, bucket_cap_mb)
         # reduce-scatter instead of all-reduce when the optimizer step is sharded: the owner
         # alone needs the averaged chunk, everybody gets the new parameters instead

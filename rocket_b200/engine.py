@@ -159,7 +159,7 @@ class Engine:
     def __init__(self, device_placement: bool = True, mixed_precision: str | None = None,
                  gradient_accumulation_steps: int = 1, project_config=None,
                  project_dir: str | None = None, *, backend=None, device=None,
-                 stage_slots: int = 3, stage_threads: int = 4, bucket_cap_mb: float = 32.0,
+                 stage_slots: int = 3, stage_threads: int = 4, bucket_cap_mb: float = 16.0,
                  stage_batches: bool = True) -> None:
         world = _env_int("WORLD_SIZE", 1)
         self.local_process_index = _env_int("LOCAL_RANK", 0)
