@@ -334,6 +334,12 @@ class EngineOptimizer:
             if max_norm is None:
                 norm = None
         groups = self._step_groups()
+        if not groups:
+            # no parameter has received a gradient yet: torch.optim skips every `grad is None`
+            # parameter, i.e. the step is a no-op
+            eng.grad_sync_step_done(self)
+            self._zeroed_by_step = True
+            return
         if self.sharded:
             # the sharded kernel always reads its constants from the device table; inside a
             # graph pass the upload moves in front of the replay (gp.pre), as for the replicated

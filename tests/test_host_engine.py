@@ -485,3 +485,25 @@ def test_save_state_writes_tied_weights_once_and_restores_them(tmp_path):
         assert torch.equal(v, want[k]), k
     assert net.out.weight.data_ptr() == net.emb.weight.data_ptr()      # still tied
     assert opt is not None
+
+
+def test_step_before_any_gradient_is_a_no_op():
+    """torch.optim skips parameters whose grad is None; a step before the first backward
+    changes nothing and counts nothing."""
+    from rocket_b200.engine import Engine
+    torch.manual_seed(0)
+    net = torch.nn.Linear(16, 16)
+    before = {k: v.clone() for k, v in net.state_dict().items()}
+    eng = Engine(backend=HostBackend(), device="cpu")
+    opt = eng.prepare(torch.optim.AdamW(net.parameters(), lr=1e-2, foreach=False))
+    with eng.accumulate(net):
+        opt.step()
+        opt.zero_grad()
+    assert all(torch.equal(v, before[k]) for k, v in net.state_dict().items())
+    assert opt._group_step == [0] and not opt.optimizer.state
+    with eng.accumulate(net):                       # and the first real step is step 1
+        eng.backward(net(torch.randn(4, 16)).square().mean())
+        opt.step()
+        opt.zero_grad()
+    assert opt._group_step == [1]
+    assert float(opt.state[net.weight]["step"]) == 1.0
