@@ -245,15 +245,17 @@ static int launch_v8(const rk_plan_header* h, const void* plan_dev, const Table&
 template <class Op, class Table, int CW>
 static int launch_bulk(const rk_plan_header* h, const void* plan_dev, const Table& table,
                        const Table* dtable, const float* total_norm_dev, float max_norm,
-                       float grad_scale, int zero_grads, void* stream, int tile, bool pdl) {
+                       float grad_scale, int zero_grads, void* stream, int tile, bool pdl,
+                       int ring_bytes = BULK_SMEM_DATA) {
   auto kernel = rk_step_bulk_kernel<Op, Table, CW>;
   RK_REQUIRE(tile >= 256 && tile <= RK_NORM_CHUNK_MIN && (tile & (tile - 1)) == 0,
              RK_ERR_INVALID, "bulk step: tile %d is not a power of two in [256, %d]", tile,
              RK_NORM_CHUNK_MIN);
   int tile_log2 = 0;
   while ((1 << tile_log2) < tile) ++tile_log2;
-  int stages = BULK_SMEM_DATA / (tile * 16);
+  int stages = ring_bytes / (tile * 16);
   if (stages > BULK_MAX_STAGES) stages = BULK_MAX_STAGES;
+  RK_REQUIRE(stages >= 2, RK_ERR_INVALID, "bulk step: ring of %d bytes holds fewer than 2 tiles", ring_bytes);
   const size_t dyn = (size_t)stages * tile * 16;
   static std::mutex mu;
   static bool configured[64];
@@ -271,10 +273,13 @@ static int launch_bulk(const rk_plan_header* h, const void* plan_dev, const Tabl
   const long long items = (long long)h->n_chunks_norm * (h->chunk_norm / tile);
   RK_REQUIRE(items < (long long)INT32_MAX, RK_ERR_TOO_LARGE,
              "bulk step: %lld tiles exceed int32", items);
-  int grid = 0;
-  int rc = rk_persistent_grid((const void*)kernel, 32 * (CW + 1), BULK_SMEM_DATA, (int)items,
-                              &grid);
-  if (rc) return rc;
+  // resident CTAs per SM depend on the ring size chosen for this launch: not cached per kernel
+  int sms = 0, per_sm = 0;
+  RK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  RK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 32 * (CW + 1), dyn));
+  RK_REQUIRE(per_sm > 0, RK_ERR_STATE, "bulk step kernel does not fit on an SM");
+  int grid = sms * per_sm;
+  if (grid > (int)items) grid = items > 0 ? (int)items : 1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(32 * (CW + 1));
@@ -369,6 +374,9 @@ static int launch_step(const void* plan_host, const void* plan_dev, const Table&
     case 23: RK_VB(12, 4096, true); break;
     case 24: RK_VB(8, 4096, true); break;
     case 25: RK_VB(16, 4096, false); break;  // as 21, ordinary stream-ordered launch
+    case 26: rc = launch_bulk<Op, Table, 8>(h, plan_dev, table, dtable, total_norm_dev, max_norm,
+                                            grad_scale, zero_grads, stream, 2048, true,
+                                            96 * 1024); break;   // two CTAs per SM, 3 x 32 KB each
 #undef RK_VB
   }
 #undef RK_V

@@ -24,7 +24,7 @@ pytestmark = pytest.mark.gpu
 VARIANTS = [(4, "v4 U2 3cta"), (9, "v4 U1 5cta"), (30, "v8 U1 3cta"), (31, "v8 U1 4cta"),
             (33, "v8 U1 5cta"), (21, "bulk 16w t4096 pdl"), (20, "bulk 16w t2048"),
             (22, "bulk 16w t1024"), (23, "bulk 12w t4096"), (24, "bulk 8w t4096"),
-            (25, "bulk 16w t4096 no-pdl")]
+            (25, "bulk 16w t4096 no-pdl"), (26, "bulk 8w t2048 2cta")]
 IDS = [f"v{v}-{name.replace(' ', '_')}" for v, name in VARIANTS]
 
 
