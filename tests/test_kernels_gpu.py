@@ -421,3 +421,44 @@ def test_adam_and_sgd_random_hyperparameters_bit_exact():
                 got = t.cpu().numpy()
                 same = (_bits(got) == _bits(a)) | (np.isnan(got) & np.isnan(a))
                 assert same.all(), ("sgd", k, d, i, name, got[~same][:4], a[~same][:4])
+
+
+def test_fifty_steps_back_to_back_without_host_syncs_bit_exact():
+    """The norm's two kernels and the step kernel are chained by programmatic dependent launch
+    (the next kernel's set-up and first loads overlap the previous one's tail).  Fifty
+    norm + step rounds queued with no host synchronisation in between -- fresh gradients
+    written on the device before each round -- must end on the oracle's bits: an ordering
+    mistake in that chain (a load of p, m or v issued too early, a norm read too early) shows
+    up as a mismatch here."""
+    be = _backend()
+    sizes = [150, 6, 2400, 16, 48000, 120, 10080, 84, 840, 10, 70001]
+    specs, host = _make_list(sizes, seed=5)
+    plan = be.make_plan(specs)
+    base = [s.g.clone() for s in specs]
+    base_h = [h[1].copy() for h in host]
+    hp = dict(ADAM_CASES[0])
+    steps = 50
+    norms = []
+    for step in range(1, steps + 1):
+        f = 1.0 + 0.03125 * (step % 7)                 # exactly representable factors
+        for s, b in zip(specs, base):
+            torch.mul(b, f, out=s.g)                   # device-side refill, stream ordered
+        norm = be.l2norm(plan, 0.5)
+        norms.append(norm.clone())                     # device copy, no sync
+        be.adam_step(plan, [dict(hp, step=step)], norm, 0.05, 0.5, True)
+    torch.cuda.synchronize()
+    for step in range(1, steps + 1):
+        f = np.float32(1.0 + 0.03125 * (step % 7))
+        tn = float(norms[step - 1].item())
+        for h, b in zip(host, base_h):
+            h[1][:] = b * f
+            oracle.adam_step(h[0], h[1], h[2], h[3], lr=hp["lr"], beta1=hp["beta1"],
+                             beta2=hp["beta2"], eps=hp["eps"], weight_decay=hp["weight_decay"],
+                             step=step, decoupled=hp["decoupled"], grad_scale=0.5,
+                             total_norm=tn, max_norm=0.05, zero_grads=True)
+        if step in (1, steps):                         # the norm itself against the oracle
+            want, _ = oracle.l2norm_multi([b * f for b in base_h], 0.5)
+            assert _ulp_diff(np.array([tn], np.float32), np.array([want], np.float32)) <= 2
+    for i, (s, h) in enumerate(zip(specs, host)):
+        for k, t in enumerate((s.p, s.g, s.m, s.v)):
+            assert np.array_equal(_bits(t.cpu().numpy()), _bits(h[k])), (i, "pgmv"[k])
