@@ -280,8 +280,10 @@ class EngineOptimizer:
             return self.last_grad_norm
         self._adopt_grads()
         plan = self._get_plan()
-        if self.engine.finish_grad_sync(self) and self.engine.scaler is None:
+        if self.engine.finish_grad_sync(self):
             norm = self.engine.backend.l2norm_finalize(plan)
+            if self.engine.scaler is not None:       # partials of loss-scaled gradients (step())
+                norm.mul_(self.engine.scaler.inv_scale)
         else:
             norm = self.engine.backend.l2norm(plan, self._read_scale())
         self._pending_clip = float(max_norm)
@@ -307,14 +309,18 @@ class EngineOptimizer:
             plan = self._get_plan()
             fused_norm = eng.finish_grad_sync(self)  # True: norm partials are in plan.scratch
             scale = self._read_scale()
-            if scaler is not None:
-                fused_norm = False     # the exchange's partials are of the loss-scaled gradients
+            # fp16 on the NVLink path: the exchange's fused partials are of the still loss-scaled
+            # (averaged) gradients.  1/scale is a power of two, so the norm of the unscaled
+            # gradients is that norm times 1/scale, exactly -- no second pass over the gradients.
+            rescale = scaler.inv_scale if (scaler is not None and fused_norm) else 1.0
             norm = None
             if max_norm is not None or scaler is not None:
                 if self._pending_clip is not None:
                     norm = self.last_grad_norm
                 elif fused_norm:
                     norm = eng.backend.l2norm_finalize(plan)
+                    if rescale != 1.0:
+                        norm.mul_(rescale)
                 else:
                     norm = eng.backend.l2norm(plan, scale)
                 self.last_grad_norm = norm

@@ -22,6 +22,12 @@ import dist_worker
 
 pytestmark = pytest.mark.gpu
 GOLDEN = Path(__file__).parent / "golden"
+# cases compared GPU against GPU only (no reference golden)
+GPU_ONLY_CASES = {
+    "ws2_fp16_adamw_clip": dict(optimizer="adamw", max_norm=0.5, accum=2, epochs=1,
+                                n_train=64 * 24, n_val=64 * 2 + 5, sched_step=3,
+                                input_scale=128.0, mixed_precision="fp16"),
+}
 
 
 def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str,
@@ -43,7 +49,7 @@ def _gpu_worker(rank: int, world: int, port: int, case: str, out_dir: str,
     engines = []
     rk.Launcher.engine_factory = staticmethod(lambda **k: engines.append(Engine(**k)) or engines[-1])
     tracker = MemoryTracker("memory")
-    kw = dict(dist_worker.WS2_CASES[case])
+    kw = dict({**dist_worker.ALL_CASES, **GPU_ONLY_CASES}[case])
     launcher, h = workloads.build_mnist_graph(
         rk, tracker_backend=tracker, clip_via="kwarg" if kw["max_norm"] else "capsule",
         accuracy_cls=Accuracy, graph=graph, **kw)
@@ -101,6 +107,28 @@ def test_fused_nvlink_allreduce_equals_nccl_path_bitwise(tmp_path):
     for k in a.files:
         if k.startswith("param/"):
             assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), k
+    assert a["loss_values"].tolist() == b["loss_values"].tolist()
+    assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("case", ["ws2_fp16_sgd", "ws2_fp16_adamw_clip"])
+def test_fp16_fused_nvlink_norm_equals_nccl_path_bitwise(case, tmp_path):
+    """mixed_precision="fp16" on two GPUs.  NVLink path: the exchange kernel's fused partials are
+    of the loss-scaled gradients; the norm of the unscaled ones (overflow check + clipping) is
+    that norm times 1/scale, a power of two.  NCCL path: a separate norm pass with the unscale
+    folded into its gradient read.  Same skipped steps, same scale, same parameters, bitwise."""
+    for i, sync in enumerate(("p2p", "nccl")):
+        mp.spawn(_gpu_worker, args=(2, 29856 + i, case, str(tmp_path), sync), nprocs=2, join=True)
+    a = np.load(tmp_path / f"{case}_p2p_rank0.npz")
+    b = np.load(tmp_path / f"{case}_nccl_rank0.npz")
+    c = np.load(tmp_path / f"{case}_p2p_rank1.npz")
+    assert len(set(a["lr_values"][:5].tolist())) == 1, "the run should start with skipped steps"
+    assert a["lr_values"].tolist() == b["lr_values"].tolist()
+    for k in a.files:
+        if k.startswith("param/"):
+            assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), k
+            assert np.array_equal(a[k].view(np.int32), c[k].view(np.int32)), k
     assert a["loss_values"].tolist() == b["loss_values"].tolist()
     assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
 
