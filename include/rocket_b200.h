@@ -282,15 +282,16 @@ int rk_comm_destroy(rk_comm* comm);
  * elements [(c / W) * chunk_norm, ... + chunk length) -- ceil(n_chunks_norm / W) * chunk_norm
  * floats each, 16-byte aligned, zero-filled before the first step -- and the plan's m / v
  * pointers are ignored (shard_v is ignored for SGD; shard_m == NULL with plan m == NULL means
- * plain SGD without momentum).  Uses barrier slot RK_COMM_MAX_BUCKETS - 1: exchanges that
+ * plain SGD without momentum).  grad_scale multiplies every gradient as it is read (1.0, or
+ * 1/loss_scale under fp16: the exchange has already averaged).  Uses barrier slot RK_COMM_MAX_BUCKETS - 1: exchanges that
  * share the communicator must use lower buckets.                                            */
 int rk_comm_reduce_scatter_norm(rk_comm* comm, const void* plan_host, const void* plan_dev,
                                 int chunk_lo, int chunk_hi, int bucket, int max_ctas,
                                 int use_multicast, void* stream);
 int rk_comm_sharded_step(rk_comm* comm, const void* plan_host, const void* plan_dev,
                          int optimizer, const void* table_dev, float* shard_m, float* shard_v,
-                         const float* total_norm_dev, float max_norm, int max_ctas,
-                         int use_multicast, void* stream);
+                         const float* total_norm_dev, float max_norm, float grad_scale,
+                         int max_ctas, int use_multicast, void* stream);
 
 /* ---- K5: pinned-ring batch stager ---------------------------------------------------
  * Replaces the blocking pageable `Tensor.to(device)` of rocket/utils/torch.py:50-51

@@ -96,7 +96,8 @@ def load() -> ctypes.CDLL:
     lib.rk_comm_destroy.argtypes = [c_void_p]
     lib.rk_comm_reduce_scatter_norm.argtypes = lib.rk_comm_allreduce_norm.argtypes
     lib.rk_comm_sharded_step.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
-                                         c_void_p, c_void_p, c_float, c_int, c_int, c_void_p]
+                                         c_void_p, c_void_p, c_float, c_float, c_int, c_int,
+                                         c_void_p]
     lib.rk_adam_table_write.argtypes = [POINTER(AdamGroup), c_int, c_void_p]
     lib.rk_sgd_table_write.argtypes = [POINTER(SgdGroup), c_int, c_void_p]
     lib.rk_adamw_step_multi_devtable.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_float,

@@ -134,13 +134,14 @@ class NativeBackend:
     # K7
     def comm_sharded_step(self, comm, plan: Plan, kind: str, table_dev_ptr: int,
                           total_norm=None, max_norm: float = 0.0, max_ctas: int = 0,
-                          use_multicast: bool = True, shard_m=None, shard_v=None) -> None:
+                          use_multicast: bool = True, shard_m=None, shard_v=None, *,
+                          grad_scale: float = 1.0) -> None:
         N.check(self.lib.rk_comm_sharded_step(
             comm, plan.host.data_ptr(), plan.dev.data_ptr(), 1 if kind == "sgd" else 0,
             table_dev_ptr, shard_m.data_ptr() if shard_m is not None else None,
             shard_v.data_ptr() if shard_v is not None else None,
             total_norm.data_ptr() if total_norm is not None else None,
-            float(max_norm), max_ctas, int(use_multicast), self._stream()),
+            float(max_norm), float(grad_scale), max_ctas, int(use_multicast), self._stream()),
             "rk_comm_sharded_step")
 
     def comm_destroy(self, comm) -> None:

@@ -385,7 +385,8 @@ __global__ void __launch_bounds__(COMM_THREADS, 3)
 rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
                        const char* __restrict__ plan, const Table* __restrict__ dtable,
                        float* __restrict__ shard_m, float* __restrict__ shard_v,
-                       const float* __restrict__ total_norm, float max_norm, int bucket) {
+                       const float* __restrict__ total_norm, float max_norm, float grad_scale,
+                       int bucket) {
   __shared__ int32_t s_prefix[RK_SMEM_PREFIX_CAP];
   const int tid = threadIdx.x;
   CommSignals* mine = reinterpret_cast<CommSignals*>(peers.arena[rank]);
@@ -398,8 +399,8 @@ rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
   const int32_t* prefix = rk_stage_prefix(
       reinterpret_cast<const int32_t*>(plan + h->off_prefix_norm), n_tensors + 1, s_prefix);
   Prolog pr;
-  pr.scale = 1.0f;
-  pr.has_scale = 0;
+  pr.scale = grad_scale;                 // 1/loss_scale under fp16 (the exchange already averaged)
+  pr.has_scale = grad_scale != 1.0f;
   pr.has_clip = total_norm != nullptr;
   pr.coef = pr.has_clip ? rk_clip_coef(__ldg(total_norm), max_norm) : 1.0f;
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -510,8 +511,8 @@ rk_sharded_step_kernel(const CommPeers peers, char* mc_arena, int rank,
 template <class Op, class Table>
 static int launch_sharded(rk_comm* c, const void* plan_host, const void* plan_dev,
                           const void* table_dev, float* shard_m, float* shard_v,
-                          const float* total_norm_dev, float max_norm, int max_ctas,
-                          int use_multicast, void* stream) {
+                          const float* total_norm_dev, float max_norm, float grad_scale,
+                          int max_ctas, int use_multicast, void* stream) {
   RK_REQUIRE(c && plan_host && plan_dev && table_dev, RK_ERR_INVALID,
              "rk_comm_sharded_step: null argument");
   RK_REQUIRE(!Op::kHasV || (shard_m == nullptr) == (shard_v == nullptr), RK_ERR_INVALID,
@@ -530,7 +531,7 @@ static int launch_sharded(rk_comm* c, const void* plan_host, const void* plan_de
 #define RK_LAUNCH(WW, MC)                                                                     \
   rk_sharded_step_kernel<Op, Table, WW, MC><<<grid, COMM_THREADS, 0, s>>>(                   \
       c->peers, c->mc_arena, c->rank, (const char*)plan_dev, (const Table*)table_dev,         \
-      shard_m, shard_v, total_norm_dev, max_norm, bucket)
+      shard_m, shard_v, total_norm_dev, max_norm, grad_scale, bucket)
   switch (c->world) {
     case 2: if (mc) RK_LAUNCH(2, true); else RK_LAUNCH(2, false); break;
     case 4: if (mc) RK_LAUNCH(4, true); else RK_LAUNCH(4, false); break;
@@ -545,14 +546,15 @@ static int launch_sharded(rk_comm* c, const void* plan_host, const void* plan_de
 extern "C" int rk_comm_sharded_step(rk_comm* c, const void* plan_host, const void* plan_dev,
                                     int optimizer, const void* table_dev, float* shard_m,
                                     float* shard_v, const float* total_norm_dev, float max_norm,
-                                    int max_ctas, int use_multicast, void* stream) {
+                                    float grad_scale, int max_ctas, int use_multicast,
+                                    void* stream) {
   if (optimizer == 0)
     return launch_sharded<AdamOp, AdamTable>(c, plan_host, plan_dev, table_dev, shard_m, shard_v,
-                                             total_norm_dev, max_norm, max_ctas, use_multicast,
+                                             total_norm_dev, max_norm, grad_scale, max_ctas, use_multicast,
                                              stream);
   if (optimizer == 1)
     return launch_sharded<SgdOp, SgdTable>(c, plan_host, plan_dev, table_dev, shard_m, shard_v,
-                                           total_norm_dev, max_norm, max_ctas, use_multicast,
+                                           total_norm_dev, max_norm, grad_scale, max_ctas, use_multicast,
                                            stream);
   RK_REQUIRE(false, RK_ERR_INVALID, "rk_comm_sharded_step: optimizer %d (0 = Adam(W), 1 = SGD)",
              optimizer);

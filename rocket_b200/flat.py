@@ -41,8 +41,6 @@ class EngineOptimizer:
         # the new parameters to all ranks.  Needs the NVLink exchange path; otherwise the step
         # stays replicated (which is what one GPU is anyway).
         self.sharded = bool(sharded) and engine.num_processes > 1 and engine.wants_p2p()
-        if self.sharded and getattr(engine, "scaler", None) is not None:
-            raise NotImplementedError("sharded optimizer step with mixed_precision='fp16'")
         self._skipped = False            # fp16: the last step overflowed and was skipped
         self.max_grad_norm: float | None = None
         self.last_grad_norm: torch.Tensor | None = None   # device scalar, for logging
@@ -364,7 +362,7 @@ class EngineOptimizer:
                 eng.backend.comm_sharded_step(
                     sync._comm, plan, self._kind, table.data_ptr(), norm,
                     float(max_norm) if max_norm is not None else 0.0, sync.step_ctas,
-                    sync.use_multicast, self.shard_m, self.shard_v)
+                    sync.use_multicast, self.shard_m, self.shard_v, grad_scale=scale)
         elif gp is None:
             fn = eng.backend.sgd_step if self._kind == "sgd" else eng.backend.adam_step
             fn(plan, groups, norm, float(max_norm) if max_norm is not None else 0.0, scale, True)

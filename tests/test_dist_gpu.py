@@ -134,6 +134,30 @@ def test_fp16_fused_nvlink_norm_equals_nccl_path_bitwise(case, tmp_path):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("case", ["ws2_fp16_sgd", "ws2_fp16_adamw_clip"])
+def test_fp16_sharded_step_equals_replicated_bitwise(case, tmp_path):
+    """mixed_precision="fp16" with Optimizer(sharded=True): the sharded kernel unscales the
+    gradients it reads (grad_scale = 1/loss_scale), the overflow check and the clip norm come
+    from the reduce-scatter's fused partials.  Skipped steps, parameters and the optimizer
+    state torch ends up holding must equal the replicated fp16 run bit for bit on both ranks."""
+    mp.spawn(_gpu_worker, args=(2, 29862, case, str(tmp_path), "p2p", False, False), nprocs=2,
+             join=True)
+    mp.spawn(_gpu_worker, args=(2, 29863, case, str(tmp_path), "p2p", False, True), nprocs=2,
+             join=True)
+    a = np.load(tmp_path / f"{case}_p2p_rank0.npz")
+    assert len(set(a["lr_values"][:5].tolist())) == 1, "the run should start with skipped steps"
+    for r in range(2):
+        b = np.load(tmp_path / f"{case}_p2p_sharded_rank{r}.npz")
+        for k in a.files:
+            if k.startswith(("param/", "state/")):
+                assert np.array_equal(a[k].view(np.int32), b[k].view(np.int32)), (r, k)
+        assert a["accuracy_history"].tolist() == b["accuracy_history"].tolist()
+    b0 = np.load(tmp_path / f"{case}_p2p_sharded_rank0.npz")
+    assert a["lr_values"].tolist() == b0["lr_values"].tolist()
+    assert a["loss_values"].tolist() == b0["loss_values"].tolist()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_graph_captured_step_with_nvlink_exchange_equals_eager(tmp_path):
     """Module(graph=True) on two GPUs: the fused NVLink exchange kernels (device-side epochs),
     the NCCL loss reduction and the optimizer step are nodes of the replayed graph; results
